@@ -1,0 +1,153 @@
+/*
+ * nbody_b200.h -- C ABI of the B200-native all-pairs N-body step.
+ *
+ * This is the drop-in boundary for the ONE hot path of LienoPC/N-BodySimulation:
+ * the O(N^2) softened-gravity step with its fused integrator.  Every entry
+ * point names the reference interface it replaces (paths relative to the
+ * reference repository root).  Plain pointers and sizes only; no CUDA, C++ or
+ * torch types.  "float4 array" below means 4 consecutive floats per body,
+ * 16-byte aligned: (x, y, z, mass) for bodies, (vx, vy, vz, pad) for
+ * velocities, (ax, ay, az, 0) for accelerations -- the reference's data model
+ * (TestProject/main.cpp:232,238-239,250-252).
+ *
+ * Error convention: every int-returning call gives 0 on success and a negative
+ * NBODY_E_* code on failure; nbody_last_error() then holds a message for the
+ * calling thread.  The reference instead throws std::runtime_error from its
+ * launcher (TestProject/kernel.cu:634,640); include/kernel.cuh converts.
+ * There is no CPU fallback: without a CUDA device every compute call fails
+ * with NBODY_E_CUDA.
+ */
+#ifndef NBODY_B200_H
+#define NBODY_B200_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NBODY_OK          0
+#define NBODY_E_INVALID  -1   /* bad argument (N <= 0, eps2 <= 0, null pointer, ...) */
+#define NBODY_E_CUDA     -2   /* a CUDA runtime call or kernel launch failed        */
+#define NBODY_E_STATE    -3   /* call not valid for this context (e.g. sharded ctx) */
+
+/* integrator arithmetic */
+#define NBODY_INTEG_F32   0   /* TestProject/kernel.cu:116-124: float, 0.5f*DT            */
+#define NBODY_INTEG_F64   1   /* Sim-Without-OpenGL-Integration/kernel.cu:71-77: double   */
+
+/* kernel variant: 0 = choose from N; others are listed by nbody_variant_info() */
+#define NBODY_VARIANT_AUTO 0
+
+typedef struct nbody_ctx nbody_ctx;
+
+/* Runtime form of TestProject/constants.h:11-13,25-26 (compile-time macros in
+ * the reference) plus the sharding a multi-GPU run needs. */
+typedef struct nbody_params {
+    int   n_bodies;      /* N: number of source bodies (all GPUs)            [N_BODIES 8192]  */
+    int   rank;          /* shard index of this context (multi-GPU)          [0]              */
+    int   world;         /* number of shards; rank g owns bodies             [1]              */
+                         /*   [g*per, min(N,(g+1)*per)), per = even ceil(N/world)             */
+    float eps2;          /* softening, added to r^2 directly; must be > 0    [EPS2 0.002f]    */
+    float dt;            /* time step                                        [DT 0.1f]        */
+    int   integrator;    /* NBODY_INTEG_F32 | NBODY_INTEG_F64                [F32]            */
+    int   device;        /* CUDA device ordinal                              [0, as kernel.cu:630] */
+    int   variant;       /* kernel variant id, NBODY_VARIANT_AUTO = pick     [0]              */
+    int   grid_ctas;     /* persistent CTAs to launch; 0 = SMs x occupancy   [0]              */
+    double eps2_f64;     /* used when integrator == F64 (headless constants.h:14)  [0.002]    */
+    double dt_f64;       /* used when integrator == F64 (headless constants.h:15)  [0.01]     */
+} nbody_params;
+
+/* Fills *p with the defaults listed above (TestProject/constants.h). */
+int nbody_params_default(nbody_params* p);
+
+/* ---- context API: state stays resident in HBM across steps ------------- */
+
+/* Replaces the allocation half of main(): TestProject/main.cpp:275-283,352-354. */
+int nbody_create(nbody_ctx** out, const nbody_params* p);
+void nbody_destroy(nbody_ctx* ctx);
+
+/* Host -> device.  x4, v4: float4[N] for ALL bodies (every shard needs all
+ * positions as sources and picks the velocities of the bodies it owns).
+ * Replaces the cudaMemcpy calls at TestProject/main.cpp:282-283,354. */
+int nbody_upload(nbody_ctx* ctx, const float* x4, const float* v4);
+
+/* Bodies owned by this context: [begin, begin+count). */
+int nbody_owned_range(nbody_ctx* ctx, int* begin, int* count);
+
+/* Device -> host of the OWNED bodies, float4[count] each (any pointer may be
+ * NULL).  The reference has no such call on its headless path (results are
+ * dropped, main.cpp:356-366); validation.cpp:79-81 does these copies by hand. */
+int nbody_download(nbody_ctx* ctx, float* x4, float* v4, float* a4);
+
+/* nsteps full steps on an unsharded context; returns after the device has
+ * finished.  Replaces simulationLoopNoVisual's loop body,
+ * TestProject/main.cpp:146-155 -> simulate(), TestProject/kernel.cu:628-645. */
+int nbody_step(nbody_ctx* ctx, int nsteps);
+
+/* Same, but only enqueued on the context's stream (no host sync). */
+int nbody_step_async(nbody_ctx* ctx, int nsteps);
+int nbody_sync(nbody_ctx* ctx);
+
+/* Device time in ms of the last nbody_step / nbody_step_async call (CUDA
+ * events on the context's stream).  The reference has no timing. */
+int nbody_elapsed_ms(nbody_ctx* ctx, float* ms);
+
+/* Kinetic energy and pair potential sum_{i<j} -m_i m_j/sqrt(r^2+eps2) of the
+ * current state, accumulated in double on the device (unsharded contexts).
+ * The scheme's conserved quantity is ke + 0.5*pe. */
+int nbody_energy(nbody_ctx* ctx, double* ke, double* pe);
+
+/* ---- sharded stepping: one context per GPU, caller owns the exchange ----
+ * Each step of rank g:
+ *   nbody_shard_local_async   : owned targets x owned sources  -> partial sums
+ *   (caller all-gathers the source buffer returned by nbody_shard_sources)
+ *   nbody_shard_remote_async  : owned targets x all other sources, integrate,
+ *                               write new owned positions into the NEXT source
+ *                               buffer, flip buffers.
+ * `stream` is a cudaStream_t passed as void* (NULL = the context's stream).  */
+int nbody_shard_local_async(nbody_ctx* ctx, void* stream);
+int nbody_shard_remote_async(nbody_ctx* ctx, void* stream);
+/* Device pointer / geometry of the packed source buffer: which = 0 current
+ * (read by the next local/remote calls), 1 = next.  slot_bytes is the size of
+ * one rank's slice (all slices equal; own slice starts at rank*slot_bytes). */
+int nbody_shard_sources(nbody_ctx* ctx, int which, void** dptr, size_t* total_bytes, size_t* slot_bytes);
+/* Geometry helper: bytes of one rank's padded slice for (N, world). */
+size_t nbody_shard_slot_bytes(int n_bodies, int world);
+
+/* ---- the reference's launch interface, as C ---------------------------- */
+
+/* What `void simulate(float4* d_bodies, float4* d_accelerations, float4*
+ * d_velocity, int N)` (TestProject/kernel.cuh:2, kernel.cu:628-645) forwards
+ * to: DEVICE pointers, one step, in place, synchronous, current device. */
+int nbody_step_inplace_f4(float* d_bodies4, float* d_accel4, float* d_vel4, int n, float eps2, float dt);
+
+/* What `void simulate(float4* bodies, float3* accelerations, float3* velocity,
+ * int N)` (Sim-Without-OpenGL-Integration/kernel.cuh:5, kernel.cu:85-125)
+ * forwards to: HOST pointers, float3 velocity, one step including the copies.
+ * As in the reference, accelerations are not returned (it zeroes them). */
+int nbody_step_host_f3(float* h_bodies4, float* h_accel3, float* h_vel3, int n, double eps2, double dt);
+
+/* Releases the per-(device, N) scratch the two calls above keep between calls. */
+void nbody_release_cached(void);
+
+/* ---- introspection ------------------------------------------------------ */
+const char* nbody_last_error(void);
+/* Kernel launches issued by this library in this process (all contexts). */
+long long nbody_launch_count(void);
+/* Describes variant `id` (1..count) into buf; returns the number of variants. */
+int nbody_variant_info(int id, char* buf, size_t buflen);
+/* Variant / grid actually used by ctx (after AUTO resolution). */
+int nbody_ctx_info(nbody_ctx* ctx, int* variant, int* grid_ctas, int* ctas_per_sm, int* sm_count);
+
+/* ---- initial conditions (host side; TestProject/utils.cpp:30-37) -------- */
+/* Reference distribution, seeded counter-based generator: positions
+ * U[-max_xyz,max_xyz]^3, mass U[min_w,max_w] (constants.h:15-19). */
+int nbody_ic_uniform(float* x4, int n, unsigned long long seed, float max_xyz, float min_w, float max_w);
+/* Plummer sphere in N-body units (M=1, a=3pi/16), velocities scaled by
+ * sqrt(1/2) for the scheme's effective G = 1/2. */
+int nbody_ic_plummer(float* x4, float* v4, int n, unsigned long long seed);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NBODY_B200_H */

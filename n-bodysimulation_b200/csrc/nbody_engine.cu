@@ -1,0 +1,330 @@
+// nbody_engine.cu -- host side of the B200 all-pairs step and its C ABI
+// (include/nbody_b200.h).  Replaces the reference's launcher
+// TestProject/kernel.cu:628-645 (simulate) and the headless-directory launcher
+// Sim-Without-OpenGL-Integration/kernel.cu:85-125; the allocation / copy
+// sequence mirrors TestProject/main.cpp:244-284,350-359.
+//
+// No CPU fallback lives here: every compute entry point needs a CUDA device.
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "../../include/nbody_b200.h"
+#include "nbody_kernels.cuh"
+
+using namespace nbody;
+
+namespace {
+
+thread_local std::string g_err;
+std::atomic<long long> g_launches{0};
+
+int fail(int code, const char* fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CU(call)                                                                          \
+    do {                                                                                  \
+        cudaError_t e_ = (call);                                                          \
+        if (e_ != cudaSuccess)                                                            \
+            return fail(NBODY_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+// ---- kernel variants -----------------------------------------------------------------------
+struct Variant {
+    int id;
+    const char* name;
+    int T, NT, UJ, unroll, packed, minb;
+    void (*kernel)(const ForceArgs);
+    size_t smem() const { return (size_t)kStages * UJ * 16 + 16 * kStages + 16; }
+    int TI() const { return T * NT; }
+};
+
+#define VARIANT(id, T, NT, UJ, UN, PK, MB) \
+    { id, "T" #T "_NT" #NT "_UJ" #UJ "_U" #UN "_" #PK "_B" #MB, T, NT, UJ, UN, PK, MB, force_kernel<T, NT, UJ, UN, (PK) != 0, MB> }
+
+// packed = FFMA2 path, 0 = scalar FFMA path (kept for the with/without evidence)
+const Variant kVariants[] = {
+    VARIANT(1, 4, 256, 256, 4, 1, 2),
+    VARIANT(2, 2, 256, 256, 4, 1, 4),
+    VARIANT(3, 2, 256, 256, 8, 1, 3),
+    VARIANT(4, 4, 128, 256, 4, 1, 4),
+    VARIANT(5, 8, 128, 256, 2, 1, 2),
+    VARIANT(6, 4, 256, 256, 8, 1, 2),
+    VARIANT(7, 4, 512, 256, 4, 1, 1),
+    VARIANT(8, 1, 256, 256, 8, 1, 6),
+    VARIANT(9, 4, 256, 256, 4, 0, 2),
+    VARIANT(10, 8, 256, 256, 2, 0, 1),
+    VARIANT(11, 2, 256, 256, 4, 0, 4),
+    VARIANT(12, 1, 128, 64, 8, 1, 8),
+    VARIANT(13, 2, 128, 128, 8, 1, 6),
+    VARIANT(14, 3, 256, 256, 4, 1, 2),
+    VARIANT(15, 6, 128, 256, 2, 1, 3),
+};
+const int kNumVariants = (int)(sizeof kVariants / sizeof kVariants[0]);
+constexpr int kSlotAlign = 512;   // bodies; multiple of every variant's UJ
+
+const Variant* find_variant(int id)
+{
+    for (int i = 0; i < kNumVariants; ++i)
+        if (kVariants[i].id == id) return &kVariants[i];
+    return nullptr;
+}
+
+int auto_variant(int n_targets, int n_sources)
+{
+    (void)n_sources;
+    if (n_targets >= 65536) return 1;
+    if (n_targets >= 8192) return 13;
+    return 12;
+}
+
+int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+// ---- launch plan for one (variant, targets, J) ---------------------------------------------------
+struct Plan {
+    int grid = 0, occ = 0, maxseg = 0, num_itiles = 0;
+    size_t partial_bytes = 0;
+};
+
+int make_plan(const Variant* v, int sm_count, int grid_override, int n_targets, int J, Plan* out)
+{
+    Plan pl;
+    CU(cudaFuncSetAttribute(v->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v->smem()));
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pl.occ, v->kernel, v->NT, v->smem()));
+    if (pl.occ < 1) return fail(NBODY_E_CUDA, "variant %s does not fit on an SM", v->name);
+    pl.num_itiles = (n_targets + v->TI() - 1) / v->TI();
+    const unsigned long long U = (unsigned long long)pl.num_itiles * (unsigned long long)J;
+    long long grid = grid_override > 0 ? grid_override : (long long)sm_count * pl.occ;
+    if ((unsigned long long)grid > U) grid = (long long)U;
+    if (grid < 1) grid = 1;
+    pl.grid = (int)grid;
+    const unsigned long long q = U / (unsigned long long)grid;   // smallest range, >= 1 when U > 0
+    pl.maxseg = q > 0 ? (int)((unsigned long long)(J - 1) / q) + 2 : 2;
+    pl.partial_bytes = (size_t)pl.num_itiles * pl.maxseg * v->TI() * sizeof(float4);
+    *out = pl;
+    return NBODY_OK;
+}
+
+int launch_force(const Variant* v, const Plan& pl, const ForceArgs& args, cudaStream_t st)
+{
+    v->kernel<<<pl.grid, v->NT, v->smem(), st>>>(args);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CU(cudaGetLastError());
+    return NBODY_OK;
+}
+
+int launch_pack(const float4* X, int n, float4* packed, int off, int n_cover, cudaStream_t st)
+{
+    if (n_cover <= 0) return NBODY_OK;
+    const int pairs = (n_cover + 1) / 2;
+    pack_kernel<<<(pairs + 255) / 256, 256, 0, st>>>(X, n, packed, off, n_cover);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CU(cudaGetLastError());
+    return NBODY_OK;
+}
+
+}  // namespace
+
+// ---- context ---------------------------------------------------------------------------------------
+struct nbody_ctx {
+    nbody_params p{};
+    int sm_count = 0;
+    const Variant* var = nullptr;
+    int n = 0, per = 0, t_begin = 0, n_targets = 0;
+    int slot_bodies = 0, n_src_pad = 0;          // packed geometry (bodies)
+    float4 *X = nullptr, *V = nullptr, *A = nullptr, *accum = nullptr;
+    float4* packed[2] = {nullptr, nullptr};
+    int cur = 0;
+    float4* partial = nullptr;
+    unsigned* counters = nullptr;
+    double* energy_part = nullptr;
+    Plan plan_full, plan_local, plan_remote;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false;
+};
+
+namespace {
+
+int per_rank(int n, int world) { return round_up((n + world - 1) / world, 2); }
+
+ForceArgs base_args(nbody_ctx* c)
+{
+    ForceArgs a{};
+    a.X = c->X; a.V = c->V; a.A = c->A;
+    a.n_targets = c->n_targets;
+    a.src = c->packed[c->cur];
+    a.partial = c->partial;
+    a.counters = c->counters;
+    a.eps2 = c->p.integrator == NBODY_INTEG_F64 ? (float)c->p.eps2_f64 : c->p.eps2;
+    a.dt = c->p.dt;
+    a.integ_f64 = c->p.integrator == NBODY_INTEG_F64;
+    a.dt64 = c->p.dt_f64;
+    return a;
+}
+
+int set_device(nbody_ctx* c)
+{
+    CU(cudaSetDevice(c->p.device));
+    return NBODY_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* nbody_last_error(void) { return g_err.c_str(); }
+long long nbody_launch_count(void) { return g_launches.load(); }
+
+int nbody_params_default(nbody_params* p)
+{
+    if (!p) return fail(NBODY_E_INVALID, "null params");
+    memset(p, 0, sizeof *p);
+    p->n_bodies = 8192;      // TestProject/constants.h:13
+    p->rank = 0; p->world = 1;
+    p->eps2 = 0.002f;        // constants.h:25
+    p->dt = 0.1f;            // constants.h:26
+    p->integrator = NBODY_INTEG_F32;
+    p->eps2_f64 = 0.002;     // Sim-Without-OpenGL-Integration/constants.h:14
+    p->dt_f64 = 0.01;        // Sim-Without-OpenGL-Integration/constants.h:15
+    return NBODY_OK;
+}
+
+int nbody_variant_info(int id, char* buf, size_t buflen)
+{
+    const Variant* v = find_variant(id);
+    if (v && buf && buflen)
+        snprintf(buf, buflen, "%s: %d targets/thread, %d threads/CTA, %d sources/tile, unroll %d pairs, %s FP32, min %d CTAs/SM, %zu B smem",
+                 v->name, v->T, v->NT, v->UJ, v->unroll, v->packed ? "packed f32x2" : "scalar", v->minb, v->smem());
+    return kNumVariants;
+}
+
+size_t nbody_shard_slot_bytes(int n_bodies, int world)
+{
+    if (n_bodies <= 0 || world <= 0) return 0;
+    return (size_t)round_up(per_rank(n_bodies, world), kSlotAlign) * sizeof(float4);
+}
+
+void nbody_destroy(nbody_ctx* c)
+{
+    if (!c) return;
+    cudaSetDevice(c->p.device);
+    cudaFree(c->X); cudaFree(c->V); cudaFree(c->A); cudaFree(c->accum);
+    cudaFree(c->packed[0]); cudaFree(c->packed[1]);
+    cudaFree(c->partial); cudaFree(c->counters); cudaFree(c->energy_part);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int nbody_create(nbody_ctx** out, const nbody_params* p)
+{
+    if (!out || !p) return fail(NBODY_E_INVALID, "null argument");
+    *out = nullptr;
+    if (p->n_bodies <= 0) return fail(NBODY_E_INVALID, "n_bodies must be > 0 (got %d)", p->n_bodies);
+    if (p->world < 1 || p->rank < 0 || p->rank >= p->world) return fail(NBODY_E_INVALID, "bad shard %d of %d", p->rank, p->world);
+    const bool f64 = p->integrator == NBODY_INTEG_F64;
+    if (!f64 && p->integrator != NBODY_INTEG_F32) return fail(NBODY_E_INVALID, "unknown integrator %d", p->integrator);
+    // the self term is 0 * m / eps2^1.5 and the zero-mass padding sits at the
+    // origin: both need eps2 > 0 to stay finite
+    if (!((f64 ? p->eps2_f64 : (double)p->eps2) > 0.0)) return fail(NBODY_E_INVALID, "eps2 must be > 0");
+    int ndev = 0;
+    CU(cudaGetDeviceCount(&ndev));
+    if (p->device < 0 || p->device >= ndev) return fail(NBODY_E_INVALID, "device %d not present (%d devices)", p->device, ndev);
+
+    nbody_ctx* c = new nbody_ctx;
+    c->p = *p;
+    int rc = set_device(c);
+    if (rc) { delete c; return rc; }
+    cudaDeviceProp prop;
+    cudaError_t e = cudaGetDeviceProperties(&prop, p->device);
+    if (e != cudaSuccess) { delete c; return fail(NBODY_E_CUDA, "cudaGetDeviceProperties: %s", cudaGetErrorString(e)); }
+    if (prop.major < 10) { delete c; return fail(NBODY_E_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", p->device, prop.major, prop.minor); }
+    c->sm_count = prop.multiProcessorCount;
+
+    c->n = p->n_bodies;
+    c->per = per_rank(c->n, p->world);
+    c->t_begin = p->rank * c->per;
+    c->n_targets = c->t_begin >= c->n ? 0 : (c->n - c->t_begin < c->per ? c->n - c->t_begin : c->per);
+    if (c->n_targets <= 0) { delete c; return fail(NBODY_E_INVALID, "shard %d of %d owns no bodies at N=%d", p->rank, p->world, p->n_bodies); }
+    c->slot_bodies = round_up(c->per, kSlotAlign);
+    c->n_src_pad = c->slot_bodies * p->world;
+
+    const int vid = p->variant == NBODY_VARIANT_AUTO ? auto_variant(c->n_targets, c->n) : p->variant;
+    c->var = find_variant(vid);
+    if (!c->var) { delete c; return fail(NBODY_E_INVALID, "unknown kernel variant %d", vid); }
+
+    const int UJ = c->var->UJ;
+    const int units_total = c->n_src_pad / UJ, units_own = c->slot_bodies / UJ;
+#define TRY(x) do { rc = (x); if (rc) { nbody_destroy(c); return rc; } } while (0)
+#define TRYCU(x) do { cudaError_t e2 = (x); if (e2 != cudaSuccess) { nbody_destroy(c); return fail(NBODY_E_CUDA, "%s: %s", #x, cudaGetErrorString(e2)); } } while (0)
+    TRY(make_plan(c->var, c->sm_count, p->grid_ctas, c->n_targets, units_total, &c->plan_full));
+    size_t partial_bytes = c->plan_full.partial_bytes;
+    if (p->world > 1) {
+        TRY(make_plan(c->var, c->sm_count, p->grid_ctas, c->n_targets, units_own, &c->plan_local));
+        TRY(make_plan(c->var, c->sm_count, p->grid_ctas, c->n_targets, units_total - units_own, &c->plan_remote));
+        if (c->plan_local.partial_bytes > partial_bytes) partial_bytes = c->plan_local.partial_bytes;
+        if (c->plan_remote.partial_bytes > partial_bytes) partial_bytes = c->plan_remote.partial_bytes;
+    }
+    const size_t tb = (size_t)c->n_targets * sizeof(float4);
+    const size_t sb = (size_t)c->n_src_pad * sizeof(float4);
+    TRYCU(cudaMalloc(&c->X, tb));
+    TRYCU(cudaMalloc(&c->V, tb));
+    TRYCU(cudaMalloc(&c->A, tb));
+    TRYCU(cudaMalloc(&c->accum, tb));
+    TRYCU(cudaMalloc(&c->packed[0], sb));
+    TRYCU(cudaMalloc(&c->packed[1], sb));
+    TRYCU(cudaMalloc(&c->partial, partial_bytes));
+    TRYCU(cudaMalloc(&c->counters, (size_t)c->plan_full.num_itiles * sizeof(unsigned)));
+    TRYCU(cudaMemset(c->V, 0, tb));
+    TRYCU(cudaMemset(c->A, 0, tb));
+    TRYCU(cudaMemset(c->packed[0], 0, sb));
+    TRYCU(cudaMemset(c->packed[1], 0, sb));
+    TRYCU(cudaMemset(c->counters, 0, (size_t)c->plan_full.num_itiles * sizeof(unsigned)));
+    TRYCU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    TRYCU(cudaEventCreate(&c->ev0));
+    TRYCU(cudaEventCreate(&c->ev1));
+    TRYCU(cudaDeviceSynchronize());
+#undef TRY
+#undef TRYCU
+    *out = c;
+    return NBODY_OK;
+}
+
+int nbody_ctx_info(nbody_ctx* c, int* variant, int* grid_ctas, int* ctas_per_sm, int* sm_count)
+{
+    if (!c) return fail(NBODY_E_INVALID, "null context");
+    if (variant) *variant = c->var->id;
+    if (grid_ctas) *grid_ctas = c->plan_full.grid;
+    if (ctas_per_sm) *ctas_per_sm = c->plan_full.occ;
+    if (sm_count) *sm_count = c->sm_count;
+    return NBODY_OK;
+}
+
+int nbody_owned_range(nbody_ctx* c, int* begin, int* count)
+{
+    if (!c) return fail(NBODY_E_INVALID, "null context");
+    if (begin) *begin = c->t_begin;
+    if (count) *count = c->n_targets;
+    return NBODY_OK;
+}
+
+}  // extern "C"
+
+#include "nbody_engine_api.inl"

@@ -1,0 +1,364 @@
+// nbody_engine_api.inl -- second half of nbody_engine.cu: data movement, stepping,
+// the reference-shaped one-call entry points and the initial conditions.
+
+namespace {
+
+// one unsharded step: all sources, fused integrate, new positions into the other buffer
+int enqueue_full_step(nbody_ctx* c, cudaStream_t st)
+{
+    ForceArgs a = base_args(c);
+    a.ra_begin = 0; a.ra_count = c->n_src_pad / c->var->UJ;
+    a.rb_begin = 0; a.rb_count = 0;
+    a.next_src = c->packed[c->cur ^ 1];
+    a.next_off = c->p.rank * c->slot_bodies;
+    a.maxseg = c->plan_full.maxseg;
+    int rc = launch_force(c->var, c->plan_full, a, st);
+    if (rc) return rc;
+    c->cur ^= 1;
+    return NBODY_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int nbody_upload(nbody_ctx* c, const float* x4, const float* v4)
+{
+    if (!c || !x4) return fail(NBODY_E_INVALID, "null argument");
+    int rc = set_device(c);
+    if (rc) return rc;
+    // stage all N positions once, pack each rank's slice into its padded slot
+    float4* stage = nullptr;
+    CU(cudaMalloc(&stage, (size_t)c->n * sizeof(float4)));
+    cudaError_t e = cudaMemcpyAsync(stage, x4, (size_t)c->n * sizeof(float4), cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(c->packed[0], 0, (size_t)c->n_src_pad * sizeof(float4), c->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(c->packed[1], 0, (size_t)c->n_src_pad * sizeof(float4), c->stream);
+    c->cur = 0;
+    for (int r = 0; r < c->p.world && e == cudaSuccess && rc == 0; ++r) {
+        const int b = r * c->per;
+        const int cnt = b >= c->n ? 0 : (c->n - b < c->per ? c->n - b : c->per);
+        if (cnt > 0) rc = launch_pack(stage + b, cnt, c->packed[0], r * c->slot_bodies, round_up(cnt, 2), c->stream);
+    }
+    if (e == cudaSuccess && rc == 0)
+        e = cudaMemcpyAsync(c->X, stage + c->t_begin, (size_t)c->n_targets * sizeof(float4), cudaMemcpyDeviceToDevice, c->stream);
+    if (e == cudaSuccess && rc == 0) {
+        if (v4) e = cudaMemcpyAsync(c->V, v4 + 4 * (size_t)c->t_begin, (size_t)c->n_targets * sizeof(float4), cudaMemcpyHostToDevice, c->stream);
+        else e = cudaMemsetAsync(c->V, 0, (size_t)c->n_targets * sizeof(float4), c->stream);
+    }
+    if (e == cudaSuccess && rc == 0) e = cudaStreamSynchronize(c->stream);
+    cudaFree(stage);
+    if (rc) return rc;
+    if (e != cudaSuccess) return fail(NBODY_E_CUDA, "upload failed: %s", cudaGetErrorString(e));
+    return NBODY_OK;
+}
+
+int nbody_download(nbody_ctx* c, float* x4, float* v4, float* a4)
+{
+    if (!c) return fail(NBODY_E_INVALID, "null context");
+    int rc = set_device(c);
+    if (rc) return rc;
+    const size_t tb = (size_t)c->n_targets * sizeof(float4);
+    CU(cudaStreamSynchronize(c->stream));
+    if (x4) CU(cudaMemcpy(x4, c->X, tb, cudaMemcpyDeviceToHost));
+    if (v4) CU(cudaMemcpy(v4, c->V, tb, cudaMemcpyDeviceToHost));
+    if (a4) CU(cudaMemcpy(a4, c->A, tb, cudaMemcpyDeviceToHost));
+    return NBODY_OK;
+}
+
+int nbody_step_async(nbody_ctx* c, int nsteps)
+{
+    if (!c) return fail(NBODY_E_INVALID, "null context");
+    if (nsteps < 0) return fail(NBODY_E_INVALID, "nsteps must be >= 0");
+    if (c->p.world != 1) return fail(NBODY_E_STATE, "nbody_step on a sharded context; use nbody_shard_*");
+    int rc = set_device(c);
+    if (rc) return rc;
+    CU(cudaEventRecord(c->ev0, c->stream));
+    for (int s = 0; s < nsteps; ++s) {
+        rc = enqueue_full_step(c, c->stream);
+        if (rc) return rc;
+    }
+    CU(cudaEventRecord(c->ev1, c->stream));
+    c->timed = true;
+    return NBODY_OK;
+}
+
+int nbody_sync(nbody_ctx* c)
+{
+    if (!c) return fail(NBODY_E_INVALID, "null context");
+    int rc = set_device(c);
+    if (rc) return rc;
+    CU(cudaStreamSynchronize(c->stream));
+    return NBODY_OK;
+}
+
+int nbody_step(nbody_ctx* c, int nsteps)
+{
+    int rc = nbody_step_async(c, nsteps);
+    if (rc) return rc;
+    return nbody_sync(c);
+}
+
+int nbody_elapsed_ms(nbody_ctx* c, float* ms)
+{
+    if (!c || !ms) return fail(NBODY_E_INVALID, "null argument");
+    if (!c->timed) return fail(NBODY_E_STATE, "no timed call yet");
+    CU(cudaEventSynchronize(c->ev1));
+    CU(cudaEventElapsedTime(ms, c->ev0, c->ev1));
+    return NBODY_OK;
+}
+
+int nbody_energy(nbody_ctx* c, double* ke, double* pe)
+{
+    if (!c || !ke || !pe) return fail(NBODY_E_INVALID, "null argument");
+    if (c->p.world != 1) return fail(NBODY_E_STATE, "nbody_energy needs an unsharded context");
+    int rc = set_device(c);
+    if (rc) return rc;
+    const int blocks = (c->n + 255) / 256;
+    if (!c->energy_part) CU(cudaMalloc(&c->energy_part, (size_t)blocks * 2 * sizeof(double)));
+    const double eps2 = c->p.integrator == NBODY_INTEG_F64 ? c->p.eps2_f64 : (double)c->p.eps2;
+    energy_kernel<<<blocks, 256, 0, c->stream>>>(c->X, c->V, c->n, eps2, c->energy_part);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CU(cudaGetLastError());
+    std::vector<double> h((size_t)blocks * 2);
+    CU(cudaMemcpyAsync(h.data(), c->energy_part, h.size() * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    double k = 0.0, p = 0.0;
+    for (int b = 0; b < blocks; ++b) { k += h[2 * b]; p += h[2 * b + 1]; }
+    *ke = k;
+    *pe = 0.5 * p;   // ordered pairs -> i<j
+    return NBODY_OK;
+}
+
+// ---- sharded stepping ---------------------------------------------------------------------------------
+int nbody_shard_sources(nbody_ctx* c, int which, void** dptr, size_t* total_bytes, size_t* slot_bytes)
+{
+    if (!c || (which != 0 && which != 1)) return fail(NBODY_E_INVALID, "bad argument");
+    if (dptr) *dptr = c->packed[c->cur ^ which];
+    if (total_bytes) *total_bytes = (size_t)c->n_src_pad * sizeof(float4);
+    if (slot_bytes) *slot_bytes = (size_t)c->slot_bodies * sizeof(float4);
+    return NBODY_OK;
+}
+
+int nbody_shard_local_async(nbody_ctx* c, void* stream)
+{
+    if (!c) return fail(NBODY_E_INVALID, "null context");
+    int rc = set_device(c);
+    if (rc) return rc;
+    cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
+    if (c->p.world == 1) return enqueue_full_step(c, st);   // nothing remote: one fused launch
+    const int UJ = c->var->UJ, own = c->slot_bodies / UJ;
+    ForceArgs a = base_args(c);
+    a.ra_begin = c->p.rank * own; a.ra_count = own;
+    a.accum_out = c->accum;
+    a.maxseg = c->plan_local.maxseg;
+    return launch_force(c->var, c->plan_local, a, st);
+}
+
+int nbody_shard_remote_async(nbody_ctx* c, void* stream)
+{
+    if (!c) return fail(NBODY_E_INVALID, "null context");
+    int rc = set_device(c);
+    if (rc) return rc;
+    if (c->p.world == 1) return NBODY_OK;
+    cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
+    const int UJ = c->var->UJ, own = c->slot_bodies / UJ, total = c->n_src_pad / UJ;
+    ForceArgs a = base_args(c);
+    a.ra_begin = 0; a.ra_count = c->p.rank * own;
+    a.rb_begin = (c->p.rank + 1) * own; a.rb_count = total - a.rb_begin;
+    a.accum_in = c->accum;
+    a.next_src = c->packed[c->cur ^ 1];
+    a.next_off = c->p.rank * c->slot_bodies;
+    a.maxseg = c->plan_remote.maxseg;
+    rc = launch_force(c->var, c->plan_remote, a, st);
+    if (rc) return rc;
+    c->cur ^= 1;
+    return NBODY_OK;
+}
+
+}  // extern "C"
+
+// ---- reference-shaped one-call entry points ------------------------------------------------------------
+namespace {
+
+struct Cached {
+    const Variant* var = nullptr;
+    Plan plan;
+    float4* packed = nullptr;
+    float4* partial = nullptr;
+    unsigned* counters = nullptr;
+    float4 *X = nullptr, *V = nullptr;   // host-pointer flavour only
+    int n_pad = 0;
+};
+std::mutex g_cache_mu;
+std::map<std::pair<int, int>, Cached> g_cache;   // (device, N)
+
+void free_cached(Cached& k)
+{
+    cudaFree(k.packed); cudaFree(k.partial); cudaFree(k.counters); cudaFree(k.X); cudaFree(k.V);
+    k = Cached();
+}
+
+int get_cached(int n, bool host_buffers, Cached** out)
+{
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    Cached& k = g_cache[std::make_pair(dev, n)];
+    if (!k.var) {
+        cudaDeviceProp prop;
+        CU(cudaGetDeviceProperties(&prop, dev));
+        if (prop.major < 10) return fail(NBODY_E_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", dev, prop.major, prop.minor);
+        k.var = find_variant(auto_variant(n, n));
+        k.n_pad = round_up(n, kSlotAlign);
+        int rc = make_plan(k.var, prop.multiProcessorCount, 0, n, k.n_pad / k.var->UJ, &k.plan);
+        if (rc) { k = Cached(); return rc; }
+        cudaError_t e = cudaMalloc(&k.packed, (size_t)k.n_pad * sizeof(float4));
+        if (e == cudaSuccess) e = cudaMalloc(&k.partial, k.plan.partial_bytes);
+        if (e == cudaSuccess) e = cudaMalloc(&k.counters, (size_t)k.plan.num_itiles * sizeof(unsigned));
+        if (e == cudaSuccess) e = cudaMemset(k.counters, 0, (size_t)k.plan.num_itiles * sizeof(unsigned));
+        if (e != cudaSuccess) { free_cached(k); return fail(NBODY_E_CUDA, "scratch allocation failed: %s", cudaGetErrorString(e)); }
+    }
+    if (host_buffers && !k.X) {
+        CU(cudaMalloc(&k.X, (size_t)n * sizeof(float4)));
+        CU(cudaMalloc(&k.V, (size_t)n * sizeof(float4)));
+    }
+    *out = &k;
+    return NBODY_OK;
+}
+
+int one_step_on_device(Cached* k, float4* dX, float4* dA, float4* dV, int n, float eps2, float dt, int f64, double dt64)
+{
+    // snapshot of the step's start in packed form; X is then advanced in place
+    int rc = launch_pack(dX, n, k->packed, 0, k->n_pad, 0);
+    if (rc) return rc;
+    ForceArgs a{};
+    a.X = dX; a.V = dV; a.A = dA;
+    a.n_targets = n;
+    a.src = k->packed;
+    a.ra_begin = 0; a.ra_count = k->n_pad / k->var->UJ;
+    a.partial = k->partial; a.counters = k->counters; a.maxseg = k->plan.maxseg;
+    a.eps2 = eps2; a.dt = dt; a.integ_f64 = f64; a.dt64 = dt64;
+    return launch_force(k->var, k->plan, a, 0);
+}
+
+}  // namespace
+
+extern "C" {
+
+int nbody_step_inplace_f4(float* d_bodies4, float* d_accel4, float* d_vel4, int n, float eps2, float dt)
+{
+    if (!d_bodies4 || !d_accel4 || !d_vel4) return fail(NBODY_E_INVALID, "null device pointer");
+    if (n <= 0) return fail(NBODY_E_INVALID, "N must be > 0 (got %d)", n);
+    if (!(eps2 > 0.f)) return fail(NBODY_E_INVALID, "eps2 must be > 0");
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    Cached* k = nullptr;
+    int rc = get_cached(n, false, &k);
+    if (rc) return rc;
+    rc = one_step_on_device(k, (float4*)d_bodies4, (float4*)d_accel4, (float4*)d_vel4, n, eps2, dt, 0, 0.0);
+    if (rc) return rc;
+    CU(cudaDeviceSynchronize());   // the reference's simulate() is synchronous (kernel.cu:644)
+    return NBODY_OK;
+}
+
+int nbody_step_host_f3(float* h_bodies4, float* h_accel3, float* h_vel3, int n, double eps2, double dt)
+{
+    (void)h_accel3;   // never copied back by the reference either (headless kernel.cu:115-124)
+    if (!h_bodies4 || !h_vel3) return fail(NBODY_E_INVALID, "null host pointer");
+    if (n <= 0) return fail(NBODY_E_INVALID, "N must be > 0 (got %d)", n);
+    if (!(eps2 > 0.0)) return fail(NBODY_E_INVALID, "eps2 must be > 0");
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    Cached* k = nullptr;
+    int rc = get_cached(n, true, &k);
+    if (rc) return rc;
+    std::vector<float> v4((size_t)n * 4, 0.f);
+    for (int i = 0; i < n; ++i) { v4[4 * (size_t)i] = h_vel3[3 * (size_t)i]; v4[4 * (size_t)i + 1] = h_vel3[3 * (size_t)i + 1]; v4[4 * (size_t)i + 2] = h_vel3[3 * (size_t)i + 2]; }
+    CU(cudaMemcpy(k->X, h_bodies4, (size_t)n * sizeof(float4), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(k->V, v4.data(), (size_t)n * sizeof(float4), cudaMemcpyHostToDevice));
+    // accelerations land in the (reused) partial-free scratch: allocate lazily next to V
+    float4* dA = nullptr;
+    CU(cudaMalloc(&dA, (size_t)n * sizeof(float4)));
+    rc = one_step_on_device(k, k->X, dA, k->V, n, (float)eps2, (float)dt, 1, dt);
+    cudaError_t e = rc ? cudaSuccess : cudaDeviceSynchronize();
+    if (!rc && e == cudaSuccess) e = cudaMemcpy(h_bodies4, k->X, (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost);
+    if (!rc && e == cudaSuccess) e = cudaMemcpy(v4.data(), k->V, (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost);
+    cudaFree(dA);
+    if (rc) return rc;
+    if (e != cudaSuccess) return fail(NBODY_E_CUDA, "host-pointer step failed: %s", cudaGetErrorString(e));
+    for (int i = 0; i < n; ++i) { h_vel3[3 * (size_t)i] = v4[4 * (size_t)i]; h_vel3[3 * (size_t)i + 1] = v4[4 * (size_t)i + 1]; h_vel3[3 * (size_t)i + 2] = v4[4 * (size_t)i + 2]; }
+    return NBODY_OK;
+}
+
+void nbody_release_cached(void)
+{
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    int cur = 0;
+    cudaGetDevice(&cur);
+    for (auto& kv : g_cache) {
+        cudaSetDevice(kv.first.first);
+        free_cached(kv.second);
+    }
+    g_cache.clear();
+    cudaSetDevice(cur);
+}
+
+// ---- initial conditions (host) -----------------------------------------------------------------------------
+static inline unsigned long long splitmix64(unsigned long long z)
+{
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+static inline double u01(unsigned long long r) { return (double)(r >> 11) * (1.0 / 9007199254740992.0); }
+
+int nbody_ic_uniform(float* x4, int n, unsigned long long seed, float max_xyz, float min_w, float max_w)
+{
+    if (!x4 || n <= 0) return fail(NBODY_E_INVALID, "bad argument");
+    for (int i = 0; i < n; ++i) {
+        const unsigned long long base = seed * 0x100000001B3ull + 4ull * (unsigned long long)i;
+        for (int c = 0; c < 3; ++c)
+            x4[4 * (size_t)i + c] = (float)((2.0 * u01(splitmix64(base + c)) - 1.0) * (double)max_xyz);
+        x4[4 * (size_t)i + 3] = (float)((double)min_w + u01(splitmix64(base + 3)) * ((double)max_w - (double)min_w));
+    }
+    return NBODY_OK;
+}
+
+int nbody_ic_plummer(float* x4, float* v4, int n, unsigned long long seed)
+{
+    if (!x4 || !v4 || n <= 0) return fail(NBODY_E_INVALID, "bad argument");
+    const double PI = 3.14159265358979323846;
+    const double rscale = 3.0 * PI / 16.0, vscale = std::sqrt(1.0 / rscale) * std::sqrt(0.5);
+    double com[3] = {0, 0, 0}, cov[3] = {0, 0, 0};
+    for (int i = 0; i < n; ++i) {
+        unsigned long long st = splitmix64(seed ^ (0xD1B54A32D192ED03ull * (unsigned long long)(i + 1)));
+        auto next = [&]() { st = splitmix64(st); return u01(st); };
+        double r;
+        do {   // Aarseth, Henon & Wielen 1974; radius cut at 10 scale lengths
+            double x1 = next();
+            if (x1 < 1e-12) x1 = 1e-12;
+            r = 1.0 / std::sqrt(std::pow(x1, -2.0 / 3.0) - 1.0);
+        } while (!(r <= 10.0));
+        auto iso = [&](double len, double* o) {
+            const double z = (1.0 - 2.0 * next()) * len, ph = 2.0 * PI * next(), s = std::sqrt(len * len - z * z);
+            o[0] = s * std::cos(ph); o[1] = s * std::sin(ph); o[2] = z;
+        };
+        double pos[3], vel[3], q, g;
+        iso(r, pos);
+        do { q = next(); g = 0.1 * next(); } while (g > q * q * std::pow(1.0 - q * q, 3.5));
+        iso(q * std::sqrt(2.0) * std::pow(1.0 + r * r, -0.25), vel);
+        for (int c = 0; c < 3; ++c) {
+            x4[4 * (size_t)i + c] = (float)(pos[c] * rscale);
+            v4[4 * (size_t)i + c] = (float)(vel[c] * vscale);
+            com[c] += x4[4 * (size_t)i + c]; cov[c] += v4[4 * (size_t)i + c];
+        }
+        x4[4 * (size_t)i + 3] = (float)(1.0 / n);
+        v4[4 * (size_t)i + 3] = 0.f;
+    }
+    for (int i = 0; i < n; ++i)
+        for (int c = 0; c < 3; ++c) {
+            x4[4 * (size_t)i + c] -= (float)(com[c] / n);
+            v4[4 * (size_t)i + c] -= (float)(cov[c] / n);
+        }
+    return NBODY_OK;
+}
+
+}  // extern "C"

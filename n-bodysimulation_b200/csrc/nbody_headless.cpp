@@ -1,0 +1,156 @@
+// nbody_headless.cpp -- the reference's headless run, restated over the engine.
+//
+// Follows TestProject/main.cpp: pinned host state (:250-252), initial
+// conditions (:254,271-272 -> utils.cpp:30-37), device copies (:275-283,352-354),
+// simulationLoopNoVisual (:142-160: `steps` calls of simulate(), exceptions ->
+// EXIT_FAILURE) and the frees (:358-366).  The three stdin prompts
+// (main.cpp:163-228) become flags; the visual branches need OpenGL and are
+// unavailable on this box.  Unlike the reference, which drops its results, the
+// driver can print a state checksum and a device-timed throughput line.
+//
+//   nbody_headless [--n N] [--steps S] [--ic reference|uniform|plummer] [--seed K]
+//                  [--eps2 E] [--dt D] [--resident] [--host-f3] [--json]
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <exception>
+#include <iostream>
+#include <string>
+
+#include "../../include/kernel.cuh"
+#include "../../include/nbody_b200.h"
+
+namespace {
+
+// TestProject/utils.cpp:6,30-37 with the unseeded rand() the reference relies on
+float random_between(float lo, float hi) { return ((float)rand() / RAND_MAX) * (hi - lo) + lo; }
+void fill_reference(float4* b, int n)
+{
+    for (int i = 0; i < n; ++i) {
+        b[i].x = random_between(-MAX_X, MAX_X);
+        b[i].y = random_between(-MAX_Y, MAX_Y);
+        b[i].z = random_between(-MAX_Z, MAX_Z);
+        b[i].w = random_between(MIN_W, MAX_W);
+    }
+}
+
+// main.cpp:142-160
+int simulationLoopNoVisual(float4* d_bodies, float4* d_accel, float4* d_vel, int n, int steps)
+{
+    printf("Starting the simulation...\n");
+    for (int counter = 0; counter < steps; ++counter) {
+        try {
+            simulate(d_bodies, d_accel, d_vel, n);
+        } catch (const std::exception& e) {
+            std::cerr << e.what() << std::endl;
+            return EXIT_FAILURE;
+        }
+    }
+    printf("Simulation complete\n");
+    return 0;
+}
+
+double checksum(const float4* v, int n)
+{
+    double s = 0;
+    for (int i = 0; i < n; ++i) s += (double)v[i].x + 2.0 * v[i].y + 3.0 * v[i].z;
+    return s;
+}
+
+}  // namespace
+
+int main(int argc, char** argv)
+{
+    int n = N_BODIES, steps = 10;
+    unsigned long long seed = 12345;
+    float eps2 = EPS2, dt = DT;
+    std::string ic = "reference";
+    bool resident = false, host_f3 = false, json = false;
+    for (int i = 1; i < argc; ++i) {
+        auto need = [&](const char* f) { if (i + 1 >= argc) { fprintf(stderr, "%s needs a value\n", f); exit(2); } return argv[++i]; };
+        if (!strcmp(argv[i], "--n")) n = atoi(need("--n"));
+        else if (!strcmp(argv[i], "--steps")) steps = atoi(need("--steps"));
+        else if (!strcmp(argv[i], "--ic")) ic = need("--ic");
+        else if (!strcmp(argv[i], "--seed")) seed = strtoull(need("--seed"), nullptr, 10);
+        else if (!strcmp(argv[i], "--eps2")) eps2 = (float)atof(need("--eps2"));
+        else if (!strcmp(argv[i], "--dt")) dt = (float)atof(need("--dt"));
+        else if (!strcmp(argv[i], "--resident")) resident = true;
+        else if (!strcmp(argv[i], "--host-f3")) host_f3 = true;
+        else if (!strcmp(argv[i], "--json")) json = true;
+        else { fprintf(stderr, "unknown flag %s\n", argv[i]); return 2; }
+    }
+    if (n <= 0 || steps < 0) { fprintf(stderr, "bad --n / --steps\n"); return 2; }
+    const size_t size4 = sizeof(float4) * (size_t)n;
+
+    float4 *bodies, *velocity, *accelerations;   // pinned, main.cpp:250-252
+    if (cudaMallocHost(&bodies, size4) != cudaSuccess || cudaMallocHost(&velocity, size4) != cudaSuccess ||
+        cudaMallocHost(&accelerations, size4) != cudaSuccess) {
+        fprintf(stderr, "cudaMallocHost failed: %s\n", cudaGetErrorString(cudaGetLastError()));
+        return EXIT_FAILURE;
+    }
+    memset(velocity, 0, size4);
+    memset(accelerations, 0, size4);
+    if (ic == "reference") fill_reference(bodies, n);
+    else if (ic == "uniform") nbody_ic_uniform((float*)bodies, n, seed, MAX_X, MIN_W, MAX_W);
+    else if (ic == "plummer") nbody_ic_plummer((float*)bodies, (float*)velocity, n, seed);
+    else { fprintf(stderr, "unknown --ic %s\n", ic.c_str()); return 2; }
+
+    int rc = 0;
+    float ms = -1.f;
+    if (host_f3) {
+        // headless-directory flavour: host pointers, float3 velocity (its constants: EPS2 0.002, DT 0.01)
+        float3* v3 = new float3[n];
+        float3* a3 = new float3[n];
+        for (int i = 0; i < n; ++i) { v3[i] = make_float3(velocity[i].x, velocity[i].y, velocity[i].z); a3[i] = make_float3(0, 0, 0); }
+        printf("Starting the simulation...\n");
+        try {
+            for (int s = 0; s < steps; ++s) simulate(bodies, a3, v3, n);
+            printf("Simulation complete\n");
+        } catch (const std::exception& e) { std::cerr << e.what() << std::endl; rc = EXIT_FAILURE; }
+        for (int i = 0; i < n; ++i) { velocity[i].x = v3[i].x; velocity[i].y = v3[i].y; velocity[i].z = v3[i].z; }
+        delete[] v3; delete[] a3;
+    } else if (resident) {
+        // state stays in HBM between steps (no per-step repack, device-timed)
+        nbody_params p;
+        nbody_params_default(&p);
+        p.n_bodies = n; p.eps2 = eps2; p.dt = dt;
+        nbody_ctx* ctx = nullptr;
+        if (nbody_create(&ctx, &p) || nbody_upload(ctx, (float*)bodies, (float*)velocity)) { std::cerr << nbody_last_error() << std::endl; return EXIT_FAILURE; }
+        printf("Starting the simulation...\n");
+        if (nbody_step(ctx, steps)) { std::cerr << nbody_last_error() << std::endl; rc = EXIT_FAILURE; }
+        else printf("Simulation complete\n");
+        nbody_elapsed_ms(ctx, &ms);
+        nbody_download(ctx, (float*)bodies, (float*)velocity, (float*)accelerations);
+        nbody_destroy(ctx);
+    } else {
+        // the reference's own sequence: main.cpp:275-283,352-356
+        float4 *d_bodies, *d_velocity, *d_accelerations;
+        cudaMalloc((void**)&d_velocity, size4);
+        cudaMalloc((void**)&d_accelerations, size4);
+        cudaMemcpy(d_velocity, velocity, size4, cudaMemcpyHostToDevice);
+        cudaMemcpy(d_accelerations, accelerations, size4, cudaMemcpyHostToDevice);
+        cudaMalloc((void**)&d_bodies, size4);
+        cudaMemcpy(d_bodies, bodies, size4, cudaMemcpyHostToDevice);
+        simulate_set_parameters(eps2, dt);
+        cudaEvent_t e0, e1;
+        cudaEventCreate(&e0); cudaEventCreate(&e1);
+        cudaEventRecord(e0);
+        rc = simulationLoopNoVisual(d_bodies, d_accelerations, d_velocity, n, steps);
+        cudaEventRecord(e1);
+        cudaEventSynchronize(e1);
+        cudaEventElapsedTime(&ms, e0, e1);
+        cudaMemcpy(bodies, d_bodies, size4, cudaMemcpyDeviceToHost);
+        cudaMemcpy(velocity, d_velocity, size4, cudaMemcpyDeviceToHost);
+        cudaMemcpy(accelerations, d_accelerations, size4, cudaMemcpyDeviceToHost);
+        cudaFree(d_bodies); cudaFree(d_velocity); cudaFree(d_accelerations);
+    }
+    if (json && rc == 0) {
+        const double inter = (double)n * (double)n * steps;
+        printf("{\"n\": %d, \"steps\": %d, \"ic\": \"%s\", \"device_ms\": %.4f, \"g_interactions_per_s\": %.3f, "
+               "\"checksum_x\": %.9e, \"checksum_v\": %.9e, \"launches\": %lld}\n",
+               n, steps, ic.c_str(), ms, ms > 0 ? inter / (ms * 1e-3) / 1e9 : 0.0, checksum(bodies, n), checksum(velocity, n), nbody_launch_count());
+    }
+    nbody_release_cached();
+    cudaFreeHost(bodies); cudaFreeHost(velocity); cudaFreeHost(accelerations);
+    return rc;
+}

@@ -1,0 +1,350 @@
+// nbody_kernels.cuh -- device code of the all-pairs step for sm_100a.
+//
+// Replaces TestProject/kernel.cu:9-29 (bodyInteractions), :55-65
+// (tile_interaction) and :80-130 (kernel) of the reference -- same physics and
+// integrator, different machine mapping:
+//   * sources live in HBM in a PACKED PAIR layout (32 B per two bodies:
+//     x0 x1 y0 y1 | z0 z1 m0 m1) so that one LDS.128 broadcast feeds the packed
+//     FP32 pipe (FADD2/FMUL2/FFMA2) two interactions per lane per instruction;
+//   * source tiles are staged by 1-D TMA bulk copies (UBLKCP) into a 4-stage
+//     shared-memory ring guarded by full/empty mbarriers;
+//   * each thread keeps T target bodies in registers;
+//   * work = (target tile) x (source unit) pairs, linearised and cut into equal
+//     contiguous ranges, one per persistent CTA ("stream-K" style), so that all
+//     148 SMs finish together at any N.  A target tile whose source range is
+//     split between CTAs is completed by the LAST CTA to arrive, which adds the
+//     partial sums in fixed segment order (deterministic) and integrates;
+//   * snapshot-pure: sources are read from the packed buffer of the step's
+//     start, new positions go to the other packed buffer.
+#pragma once
+#include "nbody_ptx.cuh"
+
+namespace nbody {
+
+constexpr int kStages = 4;           // shared-memory ring depth
+constexpr int kLookahead = kStages - 2;  // tiles in flight ahead of the consumers
+
+struct ForceArgs {
+    // owned targets, AoS float4, indexed 0..n_targets (caller-visible layout)
+    float4* X;            // (x,y,z,m)   read, then advanced in place by the owner thread
+    float4* V;            // (vx,vy,vz,w) in place, .w untouched
+    float4* A;            // (ax,ay,az,0) out
+    int n_targets;
+    // sources: packed pair layout, addressed in units of UJ bodies
+    const float4* src;    // current packed buffer
+    int ra_begin, ra_count;   // unit range A  [ra_begin, ra_begin+ra_count)
+    int rb_begin, rb_count;   // unit range B, visited after A
+    // new positions of the owned targets in packed layout (may be null)
+    float4* next_src;
+    int next_off;         // packed body index of target 0 (even)
+    // two-phase accumulation (sharded runs)
+    const float4* accum_in;   // added first when non-null
+    float4* accum_out;        // when non-null: store sums here, do not integrate
+    // split-tile fix-up scratch
+    float4* partial;      // [num_itiles][maxseg][TI]
+    unsigned* counters;   // [num_itiles], zero between launches
+    int maxseg;
+    // parameters (TestProject/constants.h:25-26 at run time)
+    float eps2, dt;
+    int integ_f64;        // 0: float integrator, 1: double (headless flavour)
+    double dt64;
+};
+
+// ---- integrator + stores for one target (TestProject/kernel.cu:116-129) -------------
+// Separately rounded multiply and add, exactly like validation.cpp:43-49 as
+// built for x86 (no FMA contraction), so that equal accelerations give
+// bit-equal positions and velocities.
+__device__ __forceinline__ void integrate_one(const ForceArgs& a, int gi, bool valid, float fx, float fy, float fz, int lane)
+{
+    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (valid) {
+        if (a.accum_in) {
+            const float4 p = a.accum_in[gi];
+            fx = __fadd_rn(p.x, fx); fy = __fadd_rn(p.y, fy); fz = __fadd_rn(p.z, fz);
+        }
+        if (a.accum_out) {
+            a.accum_out[gi] = make_float4(fx, fy, fz, 0.f);
+            return;
+        }
+        x = a.X[gi];
+        float4 v = a.V[gi];
+        if (!a.integ_f64) {
+            const float hdt = 0.5f * a.dt;
+            v.x = __fadd_rn(v.x, __fmul_rn(hdt, fx));
+            v.y = __fadd_rn(v.y, __fmul_rn(hdt, fy));
+            v.z = __fadd_rn(v.z, __fmul_rn(hdt, fz));
+            x.x = __fadd_rn(x.x, __fmul_rn(a.dt, v.x));
+            x.y = __fadd_rn(x.y, __fmul_rn(a.dt, v.y));
+            x.z = __fadd_rn(x.z, __fmul_rn(a.dt, v.z));
+        } else {
+            // Sim-Without-OpenGL-Integration/kernel.cu:71-77: 0.5 * DT * a in double
+            const double hdt = 0.5 * a.dt64;
+            v.x = (float)((double)v.x + hdt * (double)fx);
+            v.y = (float)((double)v.y + hdt * (double)fy);
+            v.z = (float)((double)v.z + hdt * (double)fz);
+            x.x = (float)((double)x.x + a.dt64 * (double)v.x);
+            x.y = (float)((double)x.y + a.dt64 * (double)v.y);
+            x.z = (float)((double)x.z + a.dt64 * (double)v.z);
+        }
+        a.X[gi] = x;
+        a.V[gi] = v;
+        a.A[gi] = make_float4(fx, fy, fz, 0.f);
+    } else if (a.accum_out) {
+        return;
+    }
+    if (a.next_src) {
+        // even lane holds body 2p, odd lane body 2p+1 (tile bases are even):
+        // exchange halves so each lane writes one 16-byte half of the pair.
+        const bool odd = lane & 1;
+        const float s0 = odd ? x.x : x.z, s1 = odd ? x.y : x.w;
+        const float r0 = __shfl_xor_sync(0xffffffffu, s0, 1);
+        const float r1 = __shfl_xor_sync(0xffffffffu, s1, 1);
+        const float4 o = odd ? make_float4(r0, x.z, r1, x.w) : make_float4(x.x, r0, x.y, r1);
+        const bool pair_valid = __shfl_xor_sync(0xffffffffu, (int)valid, 1) || valid;
+        if (pair_valid) a.next_src[(size_t)(a.next_off + gi - (int)odd) + (odd ? 1 : 0)] = o;
+    }
+}
+
+// worker that owns linear unit u when U units are cut into W equal ranges
+__device__ __forceinline__ int unit_owner(u64 u, u64 U, u64 W) { return (int)(((u + 1) * W - 1) / U); }
+
+template <int T, int NT, int UJ, int UNROLL, bool PACKED, int MINB>
+__global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
+{
+    constexpr int TI = T * NT;
+    constexpr uint32_t kStageBytes = UJ * 16;
+    static_assert((kStages & (kStages - 1)) == 0, "ring depth must be a power of two");
+    static_assert((UJ / 2) % UNROLL == 0, "unroll must divide the pairs per unit");
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const uint32_t smem_base = smem_u32(smem_raw);
+    const uint32_t bar_full = smem_base + kStages * kStageBytes;
+    const uint32_t bar_empty = bar_full + 8 * kStages;
+    volatile int* s_flag = reinterpret_cast<volatile int*>(smem_raw + kStages * kStageBytes + 16 * kStages);
+
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int J = a.ra_count + a.rb_count;
+    const int num_itiles = (a.n_targets + TI - 1) / TI;
+    const u64 U = (u64)num_itiles * (u64)J;
+    const u64 W = gridDim.x, w = blockIdx.x;
+    const u64 u_begin = w * U / W, u_end = (w + 1) * U / W;
+    const int n_fetch = (int)(u_end - u_begin);
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(bar_full + 8 * s, 1);
+            mbar_init(bar_empty + 8 * s, NT / 32);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    // ---- producer state (thread 0 only) ------------------------------------------------
+    int pj = (int)(u_begin % (u64)J);   // next source unit (index into A|B) to fetch
+    int kf = 0;                         // fetches issued so far
+    auto issue = [&]() {
+        const int s = kf & (kStages - 1), n = kf / kStages;
+        if (n > 0) mbar_wait(bar_empty + 8 * s, (n - 1) & 1);
+        const int ju = pj < a.ra_count ? a.ra_begin + pj : a.rb_begin + (pj - a.ra_count);
+        mbar_arrive_expect_tx(bar_full + 8 * s, kStageBytes);
+        tma_bulk_g2s(smem_base + s * kStageBytes, a.src + (size_t)ju * UJ, kStageBytes, bar_full + 8 * s);
+        if (++pj == J) pj = 0;
+        ++kf;
+    };
+    if (tid == 0)
+        while (kf < kLookahead && kf < n_fetch) issue();
+
+    const u64 eps2p = pack2(a.eps2, a.eps2);
+    int k = 0;   // units consumed so far
+    u64 u = u_begin;
+    while (u < u_end) {
+        const int it = (int)(u / (u64)J);
+        const int j0 = (int)(u - (u64)it * (u64)J);
+        const u64 left = u_end - u;
+        const int jn = (u64)(J - j0) < left ? (J - j0) : (int)left;
+
+        // ---- targets into registers (negated: dx = xj + (-xi) is one FADD2) ----------
+        u64 nx[T], ny[T], nz[T], ax[T], ay[T], az[T];
+        float sx[T], sy[T], sz[T], qx[T], qy[T], qz[T];   // scalar variant
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            const int gi = it * TI + tid + t * NT;
+            float4 xi = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (gi < a.n_targets) xi = a.X[gi];
+            if (PACKED) {
+                nx[t] = pack2(-xi.x, -xi.x); ny[t] = pack2(-xi.y, -xi.y); nz[t] = pack2(-xi.z, -xi.z);
+                ax[t] = 0ull; ay[t] = 0ull; az[t] = 0ull;
+            } else {
+                sx[t] = xi.x; sy[t] = xi.y; sz[t] = xi.z;
+                qx[t] = 0.f; qy[t] = 0.f; qz[t] = 0.f;
+            }
+        }
+
+        // ---- stream the source units of this segment ------------------------------------
+#pragma unroll 1
+        for (int jj = 0; jj < jn; ++jj, ++k) {
+            if (tid == 0 && kf < n_fetch) issue();
+            const int s = k & (kStages - 1);
+            mbar_wait(bar_full + 8 * s, (k / kStages) & 1);
+            const ulonglong2* sp = reinterpret_cast<const ulonglong2*>(smem_raw + s * kStageBytes);
+#pragma unroll 1
+            for (int p = 0; p < UJ / 2; p += UNROLL) {
+#pragma unroll
+                for (int q = 0; q < UNROLL; ++q) {
+                    if (PACKED) {
+                        const ulonglong2 xy = sp[2 * (p + q)];       // (x0,x1) (y0,y1)
+                        const ulonglong2 zm = sp[2 * (p + q) + 1];   // (z0,z1) (m0,m1)
+#pragma unroll
+                        for (int t = 0; t < T; ++t) {
+                            const u64 dx = add2(xy.x, nx[t]);
+                            const u64 dy = add2(xy.y, ny[t]);
+                            const u64 dz = add2(zm.x, nz[t]);
+                            u64 r2 = fma2(dx, dx, eps2p);
+                            r2 = fma2(dy, dy, r2);
+                            r2 = fma2(dz, dz, r2);
+                            const u64 d3 = mul2(mul2(r2, r2), r2);      // (r^2+eps2)^3, as kernel.cu:20
+                            float lo, hi;
+                            unpack2(d3, lo, hi);
+                            const u64 sc = mul2(pack2(rsqrt_mufu(lo), rsqrt_mufu(hi)), zm.y);
+                            ax[t] = fma2(dx, sc, ax[t]);
+                            ay[t] = fma2(dy, sc, ay[t]);
+                            az[t] = fma2(dz, sc, az[t]);
+                        }
+                    } else {
+                        const float4* sf = reinterpret_cast<const float4*>(sp);
+                        const float4 xy = sf[2 * (p + q)];
+                        const float4 zm = sf[2 * (p + q) + 1];
+#pragma unroll
+                        for (int t = 0; t < T; ++t) {
+                            {
+                                const float dx = xy.x - sx[t], dy = xy.z - sy[t], dz = zm.x - sz[t];
+                                const float r2 = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, a.eps2)));
+                                const float sc = zm.z * rsqrt_mufu(r2 * r2 * r2);
+                                qx[t] = fmaf(dx, sc, qx[t]); qy[t] = fmaf(dy, sc, qy[t]); qz[t] = fmaf(dz, sc, qz[t]);
+                            }
+                            {
+                                const float dx = xy.y - sx[t], dy = xy.w - sy[t], dz = zm.y - sz[t];
+                                const float r2 = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, a.eps2)));
+                                const float sc = zm.w * rsqrt_mufu(r2 * r2 * r2);
+                                qx[t] = fmaf(dx, sc, qx[t]); qy[t] = fmaf(dy, sc, qy[t]); qz[t] = fmaf(dz, sc, qz[t]);
+                            }
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_empty + 8 * s);
+        }
+
+        // ---- segment done: fused epilogue, or split-tile fix-up ------------------------
+        float fx[T], fy[T], fz[T];
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            if (PACKED) {
+                float lo, hi;
+                unpack2(ax[t], lo, hi); fx[t] = lo + hi;
+                unpack2(ay[t], lo, hi); fy[t] = lo + hi;
+                unpack2(az[t], lo, hi); fz[t] = lo + hi;
+            } else {
+                fx[t] = qx[t]; fy[t] = qy[t]; fz[t] = qz[t];
+            }
+        }
+        bool finish = true;
+        if (!(j0 == 0 && jn == J)) {
+            const u64 first_u = (u64)it * (u64)J;
+            const int w_first = unit_owner(first_u, U, W);
+            const int nseg = unit_owner(first_u + (u64)J - 1, U, W) - w_first + 1;
+            float4* tile_part = a.partial + (size_t)it * a.maxseg * TI;
+            float4* slot = tile_part + (size_t)((int)w - w_first) * TI;
+#pragma unroll
+            for (int t = 0; t < T; ++t) slot[tid + t * NT] = make_float4(fx[t], fy[t], fz[t], 0.f);
+            __threadfence();
+            __syncthreads();
+            if (tid == 0) {
+                const unsigned old = atomicAdd(&a.counters[it], 1u);
+                *s_flag = (old == (unsigned)(nseg - 1));
+            }
+            __syncthreads();
+            finish = (*s_flag != 0);
+            if (finish) {
+                __threadfence();
+#pragma unroll
+                for (int t = 0; t < T; ++t) { fx[t] = 0.f; fy[t] = 0.f; fz[t] = 0.f; }
+                for (int sg = 0; sg < nseg; ++sg) {
+#pragma unroll
+                    for (int t = 0; t < T; ++t) {
+                        const float4 p = __ldcg(tile_part + (size_t)sg * TI + tid + t * NT);
+                        fx[t] = __fadd_rn(fx[t], p.x); fy[t] = __fadd_rn(fy[t], p.y); fz[t] = __fadd_rn(fz[t], p.z);
+                    }
+                }
+                if (tid == 0) a.counters[it] = 0u;
+            }
+        }
+        if (finish) {
+#pragma unroll
+            for (int t = 0; t < T; ++t) {
+                const int gi = it * TI + tid + t * NT;
+                integrate_one(a, gi, gi < a.n_targets, fx[t], fy[t], fz[t], lane);
+            }
+        }
+        u += (u64)jn;
+    }
+}
+
+// ---- AoS float4 -> packed pair layout (pre-pass of the in-place API and of upload) ----
+// Covers bodies [0, n_cover) of the destination starting at packed body index
+// `off` (even); bodies >= n are written as zero-mass padding.
+__global__ void pack_kernel(const float4* __restrict__ X, int n, float4* __restrict__ packed, int off, int n_cover)
+{
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;   // pair index
+    if (2 * p >= n_cover) return;
+    const int b0 = 2 * p, b1 = 2 * p + 1;
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4 v0 = b0 < n ? X[b0] : z;
+    const float4 v1 = b1 < n ? X[b1] : z;
+    packed[(size_t)off + b0] = make_float4(v0.x, v1.x, v0.y, v1.y);
+    packed[(size_t)off + b0 + 1] = make_float4(v0.z, v1.z, v0.w, v1.w);
+}
+
+// ---- energy of the current state, double precision --------------------------------------
+// part[2*b] = kinetic, part[2*b+1] = sum over ordered pairs i!=j of -m_i m_j / sqrt(r^2+eps2)
+// (the host halves it).  Not on the step's hot path; O(N^2) in FP64.
+__global__ void __launch_bounds__(256) energy_kernel(const float4* __restrict__ X, const float4* __restrict__ V, int n, double eps2, double* __restrict__ part)
+{
+    __shared__ float4 tile[256];
+    __shared__ double red[2][256];
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    const bool valid = i < n;
+    const float4 xi = valid ? X[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+    double pe = 0.0;
+    for (int j0 = 0; j0 < n; j0 += 256) {
+        const int j = j0 + threadIdx.x;
+        tile[threadIdx.x] = j < n ? X[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+        __syncthreads();
+        const int lim = min(256, n - j0);
+        for (int jj = 0; jj < lim; ++jj) {
+            const float4 b = tile[jj];
+            const double rx = (double)b.x - (double)xi.x, ry = (double)b.y - (double)xi.y, rz = (double)b.z - (double)xi.z;
+            const double d = rx * rx + ry * ry + rz * rz + eps2;
+            if (j0 + jj != i) pe -= (double)b.w * rsqrt(d);
+        }
+        __syncthreads();
+    }
+    double ke = 0.0;
+    if (valid) {
+        const float4 v = V[i];
+        ke = 0.5 * (double)xi.w * ((double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z);
+        pe *= (double)xi.w;
+    } else {
+        pe = 0.0;
+    }
+    red[0][threadIdx.x] = ke; red[1][threadIdx.x] = pe;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (threadIdx.x < s) { red[0][threadIdx.x] += red[0][threadIdx.x + s]; red[1][threadIdx.x] += red[1][threadIdx.x + s]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { part[2 * blockIdx.x] = red[0][0]; part[2 * blockIdx.x + 1] = red[1][0]; }
+}
+
+}  // namespace nbody
