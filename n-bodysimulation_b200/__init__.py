@@ -1,0 +1,227 @@
+"""n-bodysimulation_b200 -- Python face of libnbody_b200.so (ctypes over the C ABI).
+
+The product is the CUDA library; this module only loads it and mirrors the
+reference's launch interface so tests and bench.py read like the reference's
+callers (TestProject/main.cpp:142-160, TestProject/validation.cpp:55-103):
+
+    simulate(d_bodies, d_accelerations, d_velocity, N)   # kernel.cuh:2
+    Simulation(n, ...).upload(x, v).step(k).download()   # resident state
+
+There is NO CPU fallback: if the shared library is missing the import fails,
+and every compute call fails without a CUDA device.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libnbody_b200.so")
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+        "(there is no CPU fallback for the N-body step)")
+
+lib = C.CDLL(LIB_PATH)
+
+NBODY_INTEG_F32, NBODY_INTEG_F64 = 0, 1
+
+
+class NBodyParams(C.Structure):
+    """struct nbody_params of include/nbody_b200.h (TestProject/constants.h at run time)."""
+    _fields_ = [("n_bodies", C.c_int), ("rank", C.c_int), ("world", C.c_int),
+                ("eps2", C.c_float), ("dt", C.c_float), ("integrator", C.c_int),
+                ("device", C.c_int), ("variant", C.c_int), ("grid_ctas", C.c_int),
+                ("eps2_f64", C.c_double), ("dt_f64", C.c_double)]
+
+
+_fp = C.POINTER(C.c_float)
+_vp = C.c_void_p
+# every symbol include/nbody_b200.h declares: (restype, argtypes)
+SIGNATURES = {
+    "nbody_params_default": (C.c_int, [C.POINTER(NBodyParams)]),
+    "nbody_create": (C.c_int, [C.POINTER(_vp), C.POINTER(NBodyParams)]),
+    "nbody_destroy": (None, [_vp]),
+    "nbody_upload": (C.c_int, [_vp, _vp, _vp]),
+    "nbody_owned_range": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "nbody_download": (C.c_int, [_vp, _vp, _vp, _vp]),
+    "nbody_step": (C.c_int, [_vp, C.c_int]),
+    "nbody_step_async": (C.c_int, [_vp, C.c_int]),
+    "nbody_sync": (C.c_int, [_vp]),
+    "nbody_elapsed_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
+    "nbody_energy": (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "nbody_shard_local_async": (C.c_int, [_vp, _vp]),
+    "nbody_shard_remote_async": (C.c_int, [_vp, _vp]),
+    "nbody_shard_sources": (C.c_int, [_vp, C.c_int, C.POINTER(_vp), C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
+    "nbody_shard_slot_bytes": (C.c_size_t, [C.c_int, C.c_int]),
+    "nbody_step_inplace_f4": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_float, C.c_float]),
+    "nbody_step_host_f3": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_double, C.c_double]),
+    "nbody_release_cached": (None, []),
+    "nbody_last_error": (C.c_char_p, []),
+    "nbody_launch_count": (C.c_longlong, []),
+    "nbody_variant_info": (C.c_int, [C.c_int, C.c_char_p, C.c_size_t]),
+    "nbody_ctx_info": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "nbody_ic_uniform": (C.c_int, [_vp, C.c_int, C.c_ulonglong, C.c_float, C.c_float, C.c_float]),
+    "nbody_ic_plummer": (C.c_int, [_vp, _vp, C.c_int, C.c_ulonglong]),
+}
+for _name, (_res, _args) in SIGNATURES.items():
+    _f = getattr(lib, _name)
+    _f.restype, _f.argtypes = _res, _args
+
+
+class NBodyError(RuntimeError):
+    """Python twin of the std::runtime_error the reference's launcher throws (kernel.cu:634,640)."""
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        raise NBodyError(f"[{rc}] {lib.nbody_last_error().decode()}")
+
+
+def _ptr(a) -> int:
+    """address of a C-contiguous float32 numpy array, a torch tensor, or a raw int device pointer"""
+    if a is None:
+        return 0
+    if isinstance(a, int):
+        return a
+    if isinstance(a, np.ndarray):
+        assert a.dtype == np.float32 and a.flags["C_CONTIGUOUS"], "need contiguous float32"
+        return a.ctypes.data
+    return a.data_ptr()   # torch tensor
+
+
+def launch_count() -> int:
+    return int(lib.nbody_launch_count())
+
+
+def variants() -> dict:
+    buf = C.create_string_buffer(256)
+    n = lib.nbody_variant_info(1, buf, 256)
+    out = {}
+    for i in range(1, n + 1):
+        lib.nbody_variant_info(i, buf, 256)
+        out[i] = buf.value.decode()
+    return out
+
+
+# ---- the reference's launch interface ------------------------------------------------
+_eps2, _dt = 0.002, 0.1   # TestProject/constants.h:25-26
+
+
+def simulate_set_parameters(eps2: float, dt: float) -> None:
+    global _eps2, _dt
+    _eps2, _dt = float(eps2), float(dt)
+
+
+def simulate(d_bodies, d_accelerations, d_velocity, N: int) -> None:
+    """TestProject/kernel.cuh:2 -- DEVICE float4 arrays (torch CUDA tensors or raw
+    pointers), one step in place, synchronous."""
+    _check(lib.nbody_step_inplace_f4(_ptr(d_bodies), _ptr(d_accelerations), _ptr(d_velocity), int(N), _eps2, _dt))
+
+
+def simulate_host_f3(bodies: np.ndarray, accelerations: np.ndarray, velocity: np.ndarray, N: int,
+                     eps2: float = 0.002, dt: float = 0.01) -> None:
+    """Sim-Without-OpenGL-Integration/kernel.cuh:5 -- HOST float4 bodies, float3 velocity."""
+    _check(lib.nbody_step_host_f3(_ptr(bodies), _ptr(accelerations), _ptr(velocity), int(N), eps2, dt))
+
+
+# ---- initial conditions -----------------------------------------------------------------
+def ic_uniform(n: int, seed: int = 12345, max_xyz: float = 1e5, min_w: float = 1e5, max_w: float = 1e9) -> np.ndarray:
+    x = np.zeros((n, 4), np.float32)
+    _check(lib.nbody_ic_uniform(_ptr(x), n, seed, max_xyz, min_w, max_w))
+    return x
+
+
+def ic_plummer(n: int, seed: int = 12345):
+    x = np.zeros((n, 4), np.float32)
+    v = np.zeros((n, 4), np.float32)
+    _check(lib.nbody_ic_plummer(_ptr(x), _ptr(v), n, seed))
+    return x, v
+
+
+# ---- resident-state context ----------------------------------------------------------------
+class Simulation:
+    """State resident in HBM (nbody_create .. nbody_destroy)."""
+
+    def __init__(self, n: int, eps2: float = 0.002, dt: float = 0.1, *, rank: int = 0, world: int = 1,
+                 device: int = 0, variant: int = 0, grid_ctas: int = 0, integrator: int = NBODY_INTEG_F32,
+                 eps2_f64: float = 0.002, dt_f64: float = 0.01):
+        p = NBodyParams()
+        _check(lib.nbody_params_default(C.byref(p)))
+        p.n_bodies, p.rank, p.world, p.eps2, p.dt = n, rank, world, eps2, dt
+        p.device, p.variant, p.grid_ctas, p.integrator = device, variant, grid_ctas, integrator
+        p.eps2_f64, p.dt_f64 = eps2_f64, dt_f64
+        self._h = _vp()
+        _check(lib.nbody_create(C.byref(self._h), C.byref(p)))
+        self.n = n
+        b, c = C.c_int(), C.c_int()
+        _check(lib.nbody_owned_range(self._h, C.byref(b), C.byref(c)))
+        self.begin, self.count = b.value, c.value
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            lib.nbody_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def info(self) -> dict:
+        v, g, o, s = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        _check(lib.nbody_ctx_info(self._h, C.byref(v), C.byref(g), C.byref(o), C.byref(s)))
+        return {"variant": v.value, "variant_name": variants()[v.value].split(":")[0],
+                "grid_ctas": g.value, "ctas_per_sm": o.value, "sm_count": s.value}
+
+    def upload(self, x4: np.ndarray, v4: np.ndarray | None = None) -> "Simulation":
+        assert x4.shape == (self.n, 4)
+        _check(lib.nbody_upload(self._h, _ptr(x4), _ptr(v4)))
+        return self
+
+    def step(self, nsteps: int = 1) -> "Simulation":
+        _check(lib.nbody_step(self._h, nsteps))
+        return self
+
+    def step_async(self, nsteps: int = 1) -> "Simulation":
+        _check(lib.nbody_step_async(self._h, nsteps))
+        return self
+
+    def sync(self) -> "Simulation":
+        _check(lib.nbody_sync(self._h))
+        return self
+
+    def elapsed_ms(self) -> float:
+        ms = C.c_float()
+        _check(lib.nbody_elapsed_ms(self._h, C.byref(ms)))
+        return ms.value
+
+    def download(self):
+        x = np.empty((self.count, 4), np.float32)
+        v = np.empty((self.count, 4), np.float32)
+        a = np.empty((self.count, 4), np.float32)
+        _check(lib.nbody_download(self._h, _ptr(x), _ptr(v), _ptr(a)))
+        return x, v, a
+
+    def energy(self):
+        ke, pe = C.c_double(), C.c_double()
+        _check(lib.nbody_energy(self._h, C.byref(ke), C.byref(pe)))
+        return ke.value, pe.value
+
+    # sharded stepping (one Simulation per rank; the caller owns the exchange)
+    def shard_local_async(self, stream: int = 0) -> None:
+        _check(lib.nbody_shard_local_async(self._h, stream))
+
+    def shard_remote_async(self, stream: int = 0) -> None:
+        _check(lib.nbody_shard_remote_async(self._h, stream))
+
+    def shard_sources(self, which: int = 0):
+        p, tot, slot = _vp(), C.c_size_t(), C.c_size_t()
+        _check(lib.nbody_shard_sources(self._h, which, C.byref(p), C.byref(tot), C.byref(slot)))
+        return p.value, tot.value, slot.value

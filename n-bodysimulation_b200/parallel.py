@@ -1,0 +1,97 @@
+"""parallel.py -- multi-GPU orchestration: one process per GPU, torch.distributed for
+the exchange (NCCL over NVLink on GPUs; gloo in the CPU tests of this logic).
+
+The reference is single-GPU (device 0, default stream, no
+collectives).  Sharding per BASELINE.json's north_star: rank g owns N/G target
+bodies; every step all-gathers the packed positions, overlapped with the
+interactions against the rank's own slice:
+
+    compute stream :  local(own x own) ------------------> remote(own x others)+integrate
+    comm stream    :  all_gather(new positions, in place) -^   (event)
+
+Body order and slot geometry come from the C ABI (nbody_shard_sources): rank r's
+slice sits at byte offset r*slot_bytes of the packed source buffer, so the
+in-place all-gather (`input` = own slice view of `output`) needs no staging copy.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+class DevBuf:
+    """a raw device allocation exposed through __cuda_array_interface__ (uint8), so
+    torch can view memory owned by the C library without copying"""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3, "strides": None}
+
+
+def as_tensor(ptr: int, nbytes: int, device):
+    import torch
+    return torch.as_tensor(DevBuf(ptr, nbytes), device=device)
+
+
+class ShardedSimulation:
+    """Steps a sharded run.  `sim` is this rank's nb.Simulation(rank=r, world=G) -- or any
+    object with shard_local_async / shard_remote_async / shard_sources (the gloo CPU test
+    passes a host-memory stand-in).  `group` is a torch.distributed process group."""
+
+    def __init__(self, sim, rank: int, world: int, group=None, device=None, overlap: bool = True):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.sim, self.rank, self.world, self.group = sim, rank, world, group
+        self.device = device
+        self.overlap = overlap and device is not None and torch.device(device).type == "cuda"
+        self._views = {}
+        if self.overlap:
+            self.compute = torch.cuda.Stream(device=device)
+            self.comm = torch.cuda.Stream(device=device)
+        self.steps_done = 0
+
+    def _source_views(self, which: int):
+        ptr, total, slot = self.sim.shard_sources(which)
+        key = (ptr, total)
+        if key not in self._views:
+            if isinstance(ptr, np.ndarray):          # CPU stand-in hands out a numpy buffer
+                full = self.torch.from_numpy(ptr)
+            else:
+                full = as_tensor(ptr, total, self.device)
+            self._views[key] = (full, full[self.rank * slot:(self.rank + 1) * slot])
+        return self._views[key]
+
+    def gather_current(self):
+        """all-gather the CURRENT source buffer in place (own slice -> everyone)"""
+        full, own = self._source_views(0)
+        return self.dist.all_gather_into_tensor(full, own, group=self.group, async_op=False)
+
+    def step(self) -> None:
+        """one step; on return the current source buffer holds everyone's new positions
+        (work may still be in flight on self.compute / self.comm when overlapping)"""
+        if self.world == 1:
+            self.sim.shard_local_async(self.compute.cuda_stream if self.overlap else 0)
+            self.steps_done += 1
+            return
+        if not self.overlap:
+            self.sim.shard_local_async(0)
+            self.sim.shard_remote_async(0)
+            self.gather_current()
+            self.steps_done += 1
+            return
+        torch = self.torch
+        # 1. own x own on the compute stream; needs only this rank's slice, which the previous
+        #    remote kernel (same stream) wrote -- so it runs while the gather is in flight
+        self.sim.shard_local_async(self.compute.cuda_stream)
+        # 2. own x others once the gather of the previous step has landed
+        self.compute.wait_stream(self.comm)
+        self.sim.shard_remote_async(self.compute.cuda_stream)
+        # 3. publish the new positions: in-place all-gather of the (now current) buffer
+        self.comm.wait_stream(self.compute)
+        with torch.cuda.stream(self.comm):
+            self.gather_current()
+        self.steps_done += 1
+
+    def synchronize(self) -> None:
+        if self.overlap:
+            self.compute.synchronize()
+            self.comm.synchronize()

@@ -1,0 +1,97 @@
+"""CPU tests of the drop-in boundary: the C-ABI library loads, exports every symbol
+include/nbody_b200.h declares plus the reference's mangled simulate() overloads,
+validates arguments, and refuses to compute without a CUDA device (no fallback)."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    src = open(os.path.join(ROOT, "include", "nbody_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(nbody_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol(nb):
+    names = declared_symbols()
+    assert len(names) >= 20
+    for s in names:
+        assert hasattr(nb.lib, s), f"{s} declared in include/nbody_b200.h but not exported"
+    assert set(names) == set(nb.SIGNATURES), set(names) ^ set(nb.SIGNATURES)
+
+
+def test_library_exports_reference_launch_interface(nb):
+    out = subprocess.run(["nm", "-D", "--defined-only", nb.LIB_PATH], capture_output=True, text=True, check=True).stdout
+    assert "_Z8simulateP6float4S0_S0_i" in out          # TestProject/kernel.cuh:2
+    assert "_Z8simulateP6float4P6float3S2_i" in out     # Sim-Without-OpenGL-Integration/kernel.cuh:5
+
+
+def test_params_default_are_the_reference_constants(nb):
+    p = nb.NBodyParams()
+    assert nb.lib.nbody_params_default(C.byref(p)) == 0
+    assert (p.n_bodies, p.world, p.rank) == (8192, 1, 0)                 # constants.h:13
+    assert p.eps2 == np.float32(0.002) and p.dt == np.float32(0.1)       # constants.h:25-26
+    assert (p.eps2_f64, p.dt_f64) == (0.002, 0.01)                       # headless constants.h:14-15
+
+
+def test_argument_validation(nb):
+    h = C.c_void_p()
+    p = nb.NBodyParams()
+    nb.lib.nbody_params_default(C.byref(p))
+    for field, bad in (("n_bodies", 0), ("n_bodies", -5), ("eps2", 0.0), ("world", 0), ("rank", 3), ("integrator", 7)):
+        q = nb.NBodyParams.from_buffer_copy(p)
+        setattr(q, field, bad)
+        assert nb.lib.nbody_create(C.byref(h), C.byref(q)) == -1, field
+        assert nb.lib.nbody_last_error()
+    assert nb.lib.nbody_step_inplace_f4(None, None, None, 16, 0.002, 0.1) == -1
+    assert nb.lib.nbody_step_inplace_f4(1, 1, 1, 0, 0.002, 0.1) == -1
+    assert nb.lib.nbody_step_host_f3(None, None, None, 4, 0.002, 0.01) == -1
+
+
+def test_no_cpu_fallback(nb):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("has a GPU")
+    with pytest.raises(nb.NBodyError):
+        nb.Simulation(1024)
+    x = np.zeros((8, 4), np.float32)
+    with pytest.raises(nb.NBodyError):
+        nb.simulate_host_f3(x, np.zeros((8, 3), np.float32), np.zeros((8, 3), np.float32), 8)
+
+
+def test_shard_geometry(nb):
+    f = nb.lib.nbody_shard_slot_bytes
+    assert f(1 << 20, 8) == (1 << 17) * 16
+    assert f(1000, 3) == 512 * 16          # per = 334 bodies, padded to the 512-body slot grain
+    assert f(1025, 2) == 1024 * 16         # per = 514 (even ceil) -> 1024
+    assert f(0, 1) == 0 and f(10, 0) == 0
+
+
+def test_variants_listed(nb):
+    v = nb.variants()
+    assert len(v) >= 8 and all("targets/thread" in s for s in v.values())
+
+
+def test_ic_uniform_is_seeded_and_in_range(nb):
+    a, b, c = nb.ic_uniform(4096, seed=1), nb.ic_uniform(4096, seed=1), nb.ic_uniform(4096, seed=2)
+    assert np.array_equal(a, b) and not np.array_equal(a, c)
+    assert np.abs(a[:, :3]).max() <= 1e5 and a[:, 3].min() >= 1e5 and a[:, 3].max() <= 1e9
+    assert abs(a[:, :3].mean()) < 3e3 and abs(a[:, 3].mean() - 5e8) < 2e7
+    assert np.array_equal(nb.ic_uniform(100, seed=1), a[:100])   # counter-based: prefix-stable
+
+
+def test_ic_plummer_is_a_plummer_sphere(nb, oracle):
+    x, v = nb.ic_plummer(4096, seed=3)
+    assert np.isclose(x[:, 3].sum(), 1.0, rtol=1e-5)
+    assert np.abs(x[:, :3].mean(0)).max() < 1e-6 and np.abs(v[:, :3].mean(0)).max() < 1e-6
+    r = np.linalg.norm(x[:, :3], axis=1)
+    assert 0.6 < np.median(r) / (1.3048 * 3 * np.pi / 16) < 1.4    # half-mass radius = 1.3048 a
+    ke, pe = oracle.energy(x, v, 1e-6)
+    # virial equilibrium for the scheme's effective G = 1/2: 2*KE = -0.5*PE
+    assert 0.8 < 2 * ke / (-0.5 * pe) < 1.2
