@@ -1,0 +1,204 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the oracle and the
+golden vectors made from the reference's own object code.  Tolerances are stated
+per test; all are per-body norm-relative."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+TOL_A = 1e-5     # north_star: max rel err <= 1e-5 vs validation.cpp's CPU all-pairs after 1 step
+TOL_X = 1e-6
+TOL_V = 1e-5
+
+
+def one_step(nb, x0, v0=None, **kw):
+    with nb.Simulation(len(x0), **kw) as sim:
+        sim.upload(x0, v0).step(1)
+        return sim.download()
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 31, 255, 257, 513, 1000, 2049])
+def test_ragged_sizes_match_oracle(cuda, nb, oracle, n):
+    x0 = nb.ic_uniform(n, seed=n)
+    x, v, a = one_step(nb, x0)
+    X, V, A = x0.copy(), np.zeros_like(x0), np.zeros_like(x0)
+    oracle.step_snapshot(X, A, V)
+    assert oracle.norm_rel_err(a, A) <= TOL_A
+    assert oracle.norm_rel_err(x, X) <= TOL_X and oracle.norm_rel_err(v, V) <= TOL_V
+    assert np.array_equal(x[:, 3], x0[:, 3]) and np.all(a[:, 3] == 0)     # mass kept, A.w = 0 (kernel.cu:127-129)
+
+
+def test_every_variant_matches_oracle(cuda, nb, oracle):
+    n = 3001
+    x0 = nb.ic_uniform(n, seed=11)
+    X, V, A = x0.copy(), np.zeros_like(x0), np.zeros_like(x0)
+    oracle.step_snapshot(X, A, V)
+    a64 = oracle.accel_f64(x0)
+    ref_err = oracle.norm_rel_err(A, a64)
+    for vid in nb.variants():
+        x, v, a = one_step(nb, x0, variant=vid)
+        assert oracle.norm_rel_err(a, A) <= TOL_A, vid
+        assert oracle.norm_rel_err(a, a64) <= max(TOL_A, 2 * ref_err), vid
+        assert oracle.norm_rel_err(x, X) <= TOL_X and oracle.norm_rel_err(v, V) <= TOL_V, vid
+
+
+def test_config1_n1024_10_steps_vs_reference_golden(cuda, nb, oracle, golden):
+    # BASELINE config 1: N=1024, reference ICs (fill_with_random4), 10 steps, validation.cpp CPU all-pairs
+    g = golden["steps_n1024"]
+    with nb.Simulation(1024) as sim:
+        sim.upload(g["x0"]).step(1)
+        _, _, a1 = sim.download()
+        sim.step(9)
+        x, v, a = sim.download()
+    assert oracle.norm_rel_err(a1, g["snapshot_a1"]) <= TOL_A
+    # after 10 steps rounding differences have been integrated 10 times
+    assert oracle.norm_rel_err(x, g["snapshot_x"]) <= 1e-5
+    assert oracle.norm_rel_err(v, g["snapshot_v"]) <= 1e-4
+    # the reference's own acceptance test (validation.cpp:143-164) on positions
+    assert oracle.verify_still_bodies(x, g["snapshot_x"]) == 0
+
+
+def test_config2_n16384_checked_per_step(cuda, nb, oracle):
+    n = 16384
+    x0 = nb.ic_uniform(n, seed=12345)
+    X, V, A = x0.copy(), np.zeros_like(x0), np.zeros_like(x0)
+    with nb.Simulation(n) as sim:
+        sim.upload(x0)
+        for s in range(3):
+            sim.step(1)
+            x, v, a = sim.download()
+            # re-anchor the oracle on the device state so each step is checked on its own
+            oracle.step_snapshot(X, A, V)
+            assert oracle.norm_rel_err(a, A) <= TOL_A * (1 + s), s
+            assert oracle.norm_rel_err(x, X) <= TOL_X * (1 + s), s
+            X, V = x.copy(), v.copy()
+
+
+def test_reference_launch_interface_in_place(cuda, nb, oracle):
+    torch = cuda
+    n = 5000                                                       # headless constants.h:3 N_BODIES
+    x0 = oracle.ic_reference(n)
+    dx, dv, da = torch.from_numpy(x0).cuda(), torch.zeros(n, 4, device="cuda"), torch.zeros(n, 4, device="cuda")
+    X, V, A = x0.copy(), np.zeros_like(x0), np.zeros_like(x0)
+    for _ in range(2):
+        nb.simulate(dx, da, dv, n)                                 # kernel.cuh:2
+        oracle.step_snapshot(X, A, V)
+    assert oracle.norm_rel_err(da.cpu().numpy(), A) <= 2 * TOL_A
+    assert oracle.norm_rel_err(dx.cpu().numpy(), X) <= 2 * TOL_X
+    with pytest.raises(nb.NBodyError):
+        nb.simulate(dx, da, dv, 0)
+
+
+def test_host_pointer_float3_flavour(cuda, nb, oracle):
+    n = 2048
+    x0 = oracle.ic_reference(n, max_w=1e8)                          # headless constants.h:8 MAX_W
+    xb, vb, ab = x0.copy(), np.zeros((n, 3), np.float32), np.zeros((n, 3), np.float32)
+    X, V3 = x0.copy(), np.zeros((n, 3), np.float32)
+    for _ in range(2):
+        nb.simulate_host_f3(xb, ab, vb, n)
+        oracle.step_headless_f3(X, V3, 0.002, 0.01)
+    assert oracle.norm_rel_err(xb, X) <= TOL_X and oracle.norm_rel_err(vb, V3) <= 2 * TOL_V
+
+
+def test_deterministic_and_exactly_linear_in_mass(cuda, nb):
+    n = 40000
+    x0 = nb.ic_uniform(n, seed=5)
+    _, _, a1 = one_step(nb, x0)
+    _, _, a2 = one_step(nb, x0)
+    assert np.array_equal(a1, a2)                                  # fixed summation order, no atomics on data
+    x2 = x0.copy()
+    x2[:, 3] *= 2                                                  # power-of-two scaling is exact in fp32
+    _, _, a3 = one_step(nb, x2)
+    assert np.array_equal(a3[:, :3], 2 * a1[:, :3])
+
+
+def test_split_tiles_equal_unsplit(cuda, nb, oracle):
+    # same variant, different persistent-grid sizes => different stream-K cuts; results agree to rounding
+    n = 20000
+    x0 = nb.ic_uniform(n, seed=8)
+    _, _, a_ref = one_step(nb, x0, variant=1, grid_ctas=1)
+    for g in (7, 148, 296, 1000):
+        _, _, a = one_step(nb, x0, variant=1, grid_ctas=g)
+        assert oracle.norm_rel_err(a, a_ref) <= 2e-6, g
+
+
+def test_config3_plummer_131072_energy_drift(cuda, nb, oracle):
+    n = 131072
+    x0, v0 = nb.ic_plummer(n, seed=12345)
+    idx = np.random.default_rng(0).choice(n, 256, replace=False).astype(np.int32)
+    with nb.Simulation(n, eps2=0.002, dt=0.01) as sim:
+        sim.upload(x0, v0)
+        ke0, pe0 = sim.energy()
+        sim.step(1)
+        _, _, a = sim.download()
+        a64 = oracle.accel_f64(x0, idx)
+        a32 = oracle.accel_f32(x0, idx)
+        ref_err = oracle.norm_rel_err(a32, a64)
+        assert oracle.norm_rel_err(a[idx], a64) <= max(TOL_A, 2 * ref_err)
+        sim.step(99)
+        ke1, pe1 = sim.energy()
+    e0, e1 = ke0 + 0.5 * pe0, ke1 + 0.5 * pe1                       # conserved form, SURVEY F1
+    assert abs(e1 - e0) / abs(e0) <= 1e-3
+    assert 0.8 < 2 * ke0 / (-0.5 * pe0) < 1.2                       # starts in (effective-G) virial balance
+
+
+def test_energy_kernel_matches_oracle(cuda, nb, oracle):
+    n = 3000
+    x0, v0 = nb.ic_plummer(n, seed=2)
+    with nb.Simulation(n, eps2=0.002, dt=0.01) as sim:
+        sim.upload(x0, v0)
+        ke, pe = sim.energy()
+    KE, PE = oracle.energy(x0, v0, float(np.float32(0.002)))
+    assert abs(ke - KE) <= 1e-12 * abs(KE) + 1e-18 and abs(pe - PE) <= 1e-10 * abs(PE)
+
+
+def test_config4_n1m_sampled_targets(cuda, nb, oracle):
+    n = 1 << 20
+    x0 = nb.ic_uniform(n, seed=12345)
+    idx = np.random.default_rng(1).choice(n, 128, replace=False).astype(np.int32)
+    _, _, a = one_step(nb, x0)
+    a64 = oracle.accel_f64(x0, idx)
+    ref_err = oracle.norm_rel_err(oracle.accel_f32(x0, idx), a64)
+    assert oracle.norm_rel_err(a[idx], a64) <= max(TOL_A, 2 * ref_err)
+    # momentum balance: sum m_i a_i = 0 up to rounding (size-independent property)
+    f = (a[:, :3].astype(np.float64) * x0[:, 3:4].astype(np.float64))
+    assert np.linalg.norm(f.sum(0)) <= 1e-5 * np.abs(f).sum()
+
+
+@pytest.mark.parametrize("world", [2, 3, 4])
+def test_sharded_contexts_on_one_gpu_match_unsharded(cuda, nb, oracle, world):
+    # emulates G ranks on one device, sequentially (no cross-kernel waiting): local -> exchange -> remote
+    torch = cuda
+    from importlib import import_module
+    par = import_module("n-bodysimulation_b200.parallel")
+    n = 10001
+    x0 = nb.ic_uniform(n, seed=3)
+    with nb.Simulation(n) as ref:
+        ref.upload(x0).step(3)
+        xr, vr, ar = ref.download()
+    sims = [nb.Simulation(n, rank=r, world=world) for r in range(world)]
+    try:
+        for s in sims:
+            s.upload(x0)
+        for _ in range(3):
+            for s in sims:
+                s.shard_local_async()
+            for s in sims:
+                s.shard_remote_async()
+            torch.cuda.synchronize()
+            bufs = []
+            for s in sims:
+                p, tot, slot = s.shard_sources(0)
+                bufs.append((par.as_tensor(p, tot, "cuda"), slot))
+            for r, (src, slot) in enumerate(bufs):                   # "all-gather": everyone gets rank r's slice
+                for q, (dst, _) in enumerate(bufs):
+                    if q != r:
+                        dst[r * slot:(r + 1) * slot].copy_(src[r * slot:(r + 1) * slot])
+            torch.cuda.synchronize()
+        parts = [s.download() for s in sims]
+    finally:
+        for s in sims:
+            s.close()
+    x = np.concatenate([p[0] for p in parts]); v = np.concatenate([p[1] for p in parts]); a = np.concatenate([p[2] for p in parts])
+    assert len(x) == n
+    assert oracle.norm_rel_err(a, ar) <= 3e-6 and oracle.norm_rel_err(x, xr) <= 1e-6 and oracle.norm_rel_err(v, vr) <= 3e-6
