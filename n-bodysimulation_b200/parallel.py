@@ -51,7 +51,7 @@ class ShardedSimulation:
 
     def _source_views(self, which: int):
         ptr, total, slot = self.sim.shard_sources(which)
-        key = (ptr, total)
+        key = (ptr.ctypes.data if isinstance(ptr, np.ndarray) else ptr, total)
         if key not in self._views:
             if isinstance(ptr, np.ndarray):          # CPU stand-in hands out a numpy buffer
                 full = self.torch.from_numpy(ptr)
