@@ -55,7 +55,7 @@ struct Variant {
 };
 
 #define VARIANT(id, T, NT, UJ, UN, PK, MB) \
-    { id, "T" #T "_NT" #NT "_UJ" #UJ "_U" #UN "_" #PK "_B" #MB, T, NT, UJ, UN, PK, MB, force_kernel<T, NT, UJ, UN, (PK) != 0, MB> }
+    { id, "T" #T "_NT" #NT "_UJ" #UJ "_U" #UN "_" #PK "_B" #MB, T, NT, UJ, UN, PK, MB, force_kernel<T, NT, UJ, UN, PK, MB> }
 
 // packed = FFMA2 path, 0 = scalar FFMA path (kept for the with/without evidence)
 const Variant kVariants[] = {
@@ -74,9 +74,39 @@ const Variant kVariants[] = {
     VARIANT(13, 2, 128, 128, 8, 1, 6),
     VARIANT(14, 3, 256, 256, 4, 1, 2),
     VARIANT(15, 6, 128, 256, 2, 1, 3),
+    VARIANT(16, 4, 256, 256, 4, 2, 2),
+    VARIANT(17, 4, 256, 256, 4, 3, 2),
+    VARIANT(18, 8, 128, 256, 2, 2, 2),
+    VARIANT(19, 8, 128, 256, 2, 3, 2),
+    VARIANT(20, 8, 128, 256, 4, 1, 2),
+    VARIANT(21, 8, 256, 256, 2, 1, 1),
+    VARIANT(22, 4, 192, 256, 4, 1, 3),
+    VARIANT(23, 4, 128, 256, 2, 1, 5),
+    VARIANT(24, 4, 256, 512, 4, 1, 2),
+    VARIANT(25, 4, 256, 1024, 4, 1, 2),
+    VARIANT(26, 6, 128, 256, 2, 1, 2),
+    VARIANT(27, 8, 128, 256, 1, 1, 2),
+    VARIANT(28, 8, 64, 256, 2, 1, 4),
+    VARIANT(29, 4, 320, 256, 4, 1, 2),
+    VARIANT(30, 8, 192, 256, 2, 1, 1),
+    VARIANT(31, 8, 256, 256, 1, 1, 2),
+    VARIANT(32, 8, 512, 256, 1, 1, 1),
+    VARIANT(33, 8, 512, 256, 2, 1, 1),
+    VARIANT(34, 6, 256, 256, 2, 1, 2),
+    VARIANT(35, 6, 512, 256, 2, 1, 1),
+    VARIANT(36, 5, 256, 256, 2, 1, 2),
+    VARIANT(37, 8, 256, 256, 4, 1, 1),
+    VARIANT(38, 8, 384, 256, 2, 1, 1),
+    VARIANT(39, 12, 128, 256, 1, 1, 2),
+    VARIANT(40, 12, 256, 256, 1, 1, 1),
+    VARIANT(41, 16, 128, 256, 1, 1, 2),
+    VARIANT(42, 16, 256, 256, 1, 1, 1),
+    VARIANT(43, 10, 256, 256, 1, 1, 1),
+    VARIANT(44, 8, 256, 512, 2, 1, 1),
+    VARIANT(45, 6, 256, 256, 2, 1, 1),
 };
 const int kNumVariants = (int)(sizeof kVariants / sizeof kVariants[0]);
-constexpr int kSlotAlign = 512;   // bodies; multiple of every variant's UJ
+constexpr int kSlotAlign = 1024;   // bodies; multiple of every variant's UJ
 
 const Variant* find_variant(int id)
 {
@@ -88,7 +118,7 @@ const Variant* find_variant(int id)
 int auto_variant(int n_targets, int n_sources)
 {
     (void)n_sources;
-    if (n_targets >= 65536) return 1;
+    if (n_targets >= 65536) return 45;   // T6 x 256 threads, 1 CTA/SM: best of the r1 sweeps (profiles/)
     if (n_targets >= 8192) return 13;
     return 12;
 }
@@ -120,8 +150,11 @@ int make_plan(const Variant* v, int sm_count, int grid_override, int n_targets, 
     return NBODY_OK;
 }
 
-int launch_force(const Variant* v, const Plan& pl, const ForceArgs& args, cudaStream_t st)
+int launch_force(const Variant* v, const Plan& pl, const ForceArgs& args_in, cudaStream_t st)
 {
+    ForceArgs args = args_in;
+    args.k_one = 1.0f;
+    args.k_negzero = -0.0f;
     v->kernel<<<pl.grid, v->NT, v->smem(), st>>>(args);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     CU(cudaGetLastError());
@@ -210,7 +243,7 @@ int nbody_variant_info(int id, char* buf, size_t buflen)
     const Variant* v = find_variant(id);
     if (v && buf && buflen)
         snprintf(buf, buflen, "%s: %d targets/thread, %d threads/CTA, %d sources/tile, unroll %d pairs, %s FP32, min %d CTAs/SM, %zu B smem",
-                 v->name, v->T, v->NT, v->UJ, v->unroll, v->packed ? "packed f32x2" : "scalar", v->minb, v->smem());
+                 v->name, v->T, v->NT, v->UJ, v->unroll, v->packed == 0 ? "scalar" : v->packed == 1 ? "packed f32x2" : v->packed == 2 ? "packed f32x2 (all FFMA2)" : "packed f32x2 + prefetch", v->minb, v->smem());
     return kNumVariants;
 }
 

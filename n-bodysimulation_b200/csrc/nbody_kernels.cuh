@@ -48,6 +48,7 @@ struct ForceArgs {
     float eps2, dt;
     int integ_f64;        // 0: float integrator, 1: double (headless flavour)
     double dt64;
+    float k_one, k_negzero;   // 1.0f and -0.0f as run-time values (MODE 2 keeps ptxas from folding x*1+y)
 };
 
 // ---- integrator + stores for one target (TestProject/kernel.cu:116-129) -------------
@@ -108,9 +109,12 @@ __device__ __forceinline__ void integrate_one(const ForceArgs& a, int gi, bool v
 // worker that owns linear unit u when U units are cut into W equal ranges
 __device__ __forceinline__ int unit_owner(u64 u, u64 U, u64 W) { return (int)(((u + 1) * W - 1) / U); }
 
-template <int T, int NT, int UJ, int UNROLL, bool PACKED, int MINB>
+// MODE: 0 scalar FFMA | 1 packed FADD2/FMUL2/FFMA2 | 2 packed, every op issued as FFMA2
+//       (x*1+y, x*y-0: bit-identical results) | 3 packed + source pairs prefetched one group ahead
+template <int T, int NT, int UJ, int UNROLL, int MODE, int MINB>
 __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
 {
+    constexpr bool PACKED = MODE != 0;
     constexpr int TI = T * NT;
     constexpr uint32_t kStageBytes = UJ * 16;
     static_assert((kStages & (kStages - 1)) == 0, "ring depth must be a power of two");
@@ -187,29 +191,50 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
             const int s = k & (kStages - 1);
             mbar_wait(bar_full + 8 * s, (k / kStages) & 1);
             const ulonglong2* sp = reinterpret_cast<const ulonglong2*>(smem_raw + s * kStageBytes);
+            const u64 one2 = pack2(a.k_one, a.k_one), negz2 = pack2(a.k_negzero, a.k_negzero);
+            auto ADD2 = [&](u64 x, u64 y) { return MODE == 2 ? fma2(x, one2, y) : add2(x, y); };
+            auto MUL2 = [&](u64 x, u64 y) { return MODE == 2 ? fma2(x, y, negz2) : mul2(x, y); };
+            // two interactions (one source pair) against every target held by this thread
+            auto interact2 = [&](const ulonglong2 xy, const ulonglong2 zm) {
+#pragma unroll
+                for (int t = 0; t < T; ++t) {
+                    const u64 dx = ADD2(xy.x, nx[t]);
+                    const u64 dy = ADD2(xy.y, ny[t]);
+                    const u64 dz = ADD2(zm.x, nz[t]);
+                    u64 r2 = fma2(dx, dx, eps2p);
+                    r2 = fma2(dy, dy, r2);
+                    r2 = fma2(dz, dz, r2);
+                    const u64 d3 = MUL2(MUL2(r2, r2), r2);      // (r^2+eps2)^3, as kernel.cu:20
+                    float lo, hi;
+                    unpack2(d3, lo, hi);
+                    const u64 sc = MUL2(pack2(rsqrt_mufu(lo), rsqrt_mufu(hi)), zm.y);
+                    ax[t] = fma2(dx, sc, ax[t]);
+                    ay[t] = fma2(dy, sc, ay[t]);
+                    az[t] = fma2(dz, sc, az[t]);
+                }
+            };
+            if (MODE == 3) {
+                ulonglong2 cxy[UNROLL], czm[UNROLL];
+#pragma unroll
+                for (int q = 0; q < UNROLL; ++q) { cxy[q] = sp[2 * q]; czm[q] = sp[2 * q + 1]; }
+#pragma unroll 1
+                for (int p = 0; p < UJ / 2; p += UNROLL) {
+                    ulonglong2 nxy[UNROLL], nzm[UNROLL];
+                    const int pn = (p + UNROLL < UJ / 2) ? p + UNROLL : p;   // last group re-reads itself
+#pragma unroll
+                    for (int q = 0; q < UNROLL; ++q) { nxy[q] = sp[2 * (pn + q)]; nzm[q] = sp[2 * (pn + q) + 1]; }
+#pragma unroll
+                    for (int q = 0; q < UNROLL; ++q) interact2(cxy[q], czm[q]);
+#pragma unroll
+                    for (int q = 0; q < UNROLL; ++q) { cxy[q] = nxy[q]; czm[q] = nzm[q]; }
+                }
+            } else {
 #pragma unroll 1
             for (int p = 0; p < UJ / 2; p += UNROLL) {
 #pragma unroll
                 for (int q = 0; q < UNROLL; ++q) {
                     if (PACKED) {
-                        const ulonglong2 xy = sp[2 * (p + q)];       // (x0,x1) (y0,y1)
-                        const ulonglong2 zm = sp[2 * (p + q) + 1];   // (z0,z1) (m0,m1)
-#pragma unroll
-                        for (int t = 0; t < T; ++t) {
-                            const u64 dx = add2(xy.x, nx[t]);
-                            const u64 dy = add2(xy.y, ny[t]);
-                            const u64 dz = add2(zm.x, nz[t]);
-                            u64 r2 = fma2(dx, dx, eps2p);
-                            r2 = fma2(dy, dy, r2);
-                            r2 = fma2(dz, dz, r2);
-                            const u64 d3 = mul2(mul2(r2, r2), r2);      // (r^2+eps2)^3, as kernel.cu:20
-                            float lo, hi;
-                            unpack2(d3, lo, hi);
-                            const u64 sc = mul2(pack2(rsqrt_mufu(lo), rsqrt_mufu(hi)), zm.y);
-                            ax[t] = fma2(dx, sc, ax[t]);
-                            ay[t] = fma2(dy, sc, ay[t]);
-                            az[t] = fma2(dz, sc, az[t]);
-                        }
+                        interact2(sp[2 * (p + q)], sp[2 * (p + q) + 1]);   // (x0,x1)(y0,y1) | (z0,z1)(m0,m1)
                     } else {
                         const float4* sf = reinterpret_cast<const float4*>(sp);
                         const float4 xy = sf[2 * (p + q)];
@@ -231,6 +256,7 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
                         }
                     }
                 }
+            }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_empty + 8 * s);

@@ -68,7 +68,7 @@ def test_no_cpu_fallback(nb):
 def test_shard_geometry(nb):
     f = nb.lib.nbody_shard_slot_bytes
     assert f(1 << 20, 8) == (1 << 17) * 16
-    assert f(1000, 3) == 512 * 16          # per = 334 bodies, padded to the 512-body slot grain
+    assert f(1000, 3) == 1024 * 16         # per = 334 bodies, padded to the 1024-body slot grain
     assert f(1025, 2) == 1024 * 16         # per = 514 (even ceil) -> 1024
     assert f(0, 1) == 0 and f(10, 0) == 0
 
