@@ -162,7 +162,7 @@ class Simulation:
         self.begin, self.count = b.value, c.value
 
     def close(self) -> None:
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:
             lib.nbody_destroy(self._h)
             self._h = None
 

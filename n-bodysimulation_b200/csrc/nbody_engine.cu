@@ -186,6 +186,7 @@ struct nbody_ctx {
     float4* partial = nullptr;
     unsigned* counters = nullptr;
     double* energy_part = nullptr;
+    float4* stage = nullptr;                     // upload staging, float4[n]
     Plan plan_full, plan_local, plan_remote;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -259,7 +260,7 @@ void nbody_destroy(nbody_ctx* c)
     cudaSetDevice(c->p.device);
     cudaFree(c->X); cudaFree(c->V); cudaFree(c->A); cudaFree(c->accum);
     cudaFree(c->packed[0]); cudaFree(c->packed[1]);
-    cudaFree(c->partial); cudaFree(c->counters); cudaFree(c->energy_part);
+    cudaFree(c->partial); cudaFree(c->counters); cudaFree(c->energy_part); cudaFree(c->stage);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -321,6 +322,7 @@ int nbody_create(nbody_ctx** out, const nbody_params* p)
     TRYCU(cudaMalloc(&c->V, tb));
     TRYCU(cudaMalloc(&c->A, tb));
     TRYCU(cudaMalloc(&c->accum, tb));
+    TRYCU(cudaMalloc(&c->stage, (size_t)c->n * sizeof(float4)));
     TRYCU(cudaMalloc(&c->packed[0], sb));
     TRYCU(cudaMalloc(&c->packed[1], sb));
     TRYCU(cudaMalloc(&c->partial, partial_bytes));

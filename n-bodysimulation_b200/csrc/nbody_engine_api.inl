@@ -28,8 +28,7 @@ int nbody_upload(nbody_ctx* c, const float* x4, const float* v4)
     int rc = set_device(c);
     if (rc) return rc;
     // stage all N positions once, pack each rank's slice into its padded slot
-    float4* stage = nullptr;
-    CU(cudaMalloc(&stage, (size_t)c->n * sizeof(float4)));
+    float4* stage = c->stage;   // persistent: a cudaMalloc/cudaFree per call costs up to 100 ms (profiles/r1 notes)
     cudaError_t e = cudaMemcpyAsync(stage, x4, (size_t)c->n * sizeof(float4), cudaMemcpyHostToDevice, c->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(c->packed[0], 0, (size_t)c->n_src_pad * sizeof(float4), c->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(c->packed[1], 0, (size_t)c->n_src_pad * sizeof(float4), c->stream);
@@ -46,7 +45,6 @@ int nbody_upload(nbody_ctx* c, const float* x4, const float* v4)
         else e = cudaMemsetAsync(c->V, 0, (size_t)c->n_targets * sizeof(float4), c->stream);
     }
     if (e == cudaSuccess && rc == 0) e = cudaStreamSynchronize(c->stream);
-    cudaFree(stage);
     if (rc) return rc;
     if (e != cudaSuccess) return fail(NBODY_E_CUDA, "upload failed: %s", cudaGetErrorString(e));
     return NBODY_OK;
@@ -186,7 +184,7 @@ struct Cached {
     float4* packed = nullptr;
     float4* partial = nullptr;
     unsigned* counters = nullptr;
-    float4 *X = nullptr, *V = nullptr;   // host-pointer flavour only
+    float4 *X = nullptr, *V = nullptr, *A = nullptr;   // host-pointer flavour only
     int n_pad = 0;
 };
 std::mutex g_cache_mu;
@@ -194,7 +192,7 @@ std::map<std::pair<int, int>, Cached> g_cache;   // (device, N)
 
 void free_cached(Cached& k)
 {
-    cudaFree(k.packed); cudaFree(k.partial); cudaFree(k.counters); cudaFree(k.X); cudaFree(k.V);
+    cudaFree(k.packed); cudaFree(k.partial); cudaFree(k.counters); cudaFree(k.X); cudaFree(k.V); cudaFree(k.A);
     k = Cached();
 }
 
@@ -220,6 +218,7 @@ int get_cached(int n, bool host_buffers, Cached** out)
     if (host_buffers && !k.X) {
         CU(cudaMalloc(&k.X, (size_t)n * sizeof(float4)));
         CU(cudaMalloc(&k.V, (size_t)n * sizeof(float4)));
+        CU(cudaMalloc(&k.A, (size_t)n * sizeof(float4)));
     }
     *out = &k;
     return NBODY_OK;
@@ -273,14 +272,11 @@ int nbody_step_host_f3(float* h_bodies4, float* h_accel3, float* h_vel3, int n, 
     for (int i = 0; i < n; ++i) { v4[4 * (size_t)i] = h_vel3[3 * (size_t)i]; v4[4 * (size_t)i + 1] = h_vel3[3 * (size_t)i + 1]; v4[4 * (size_t)i + 2] = h_vel3[3 * (size_t)i + 2]; }
     CU(cudaMemcpy(k->X, h_bodies4, (size_t)n * sizeof(float4), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(k->V, v4.data(), (size_t)n * sizeof(float4), cudaMemcpyHostToDevice));
-    // accelerations land in the (reused) partial-free scratch: allocate lazily next to V
-    float4* dA = nullptr;
-    CU(cudaMalloc(&dA, (size_t)n * sizeof(float4)));
+    float4* dA = k->A;
     rc = one_step_on_device(k, k->X, dA, k->V, n, (float)eps2, (float)dt, 1, dt);
     cudaError_t e = rc ? cudaSuccess : cudaDeviceSynchronize();
     if (!rc && e == cudaSuccess) e = cudaMemcpy(h_bodies4, k->X, (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost);
     if (!rc && e == cudaSuccess) e = cudaMemcpy(v4.data(), k->V, (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost);
-    cudaFree(dA);
     if (rc) return rc;
     if (e != cudaSuccess) return fail(NBODY_E_CUDA, "host-pointer step failed: %s", cudaGetErrorString(e));
     for (int i = 0; i < n; ++i) { h_vel3[3 * (size_t)i] = v4[4 * (size_t)i]; h_vel3[3 * (size_t)i + 1] = v4[4 * (size_t)i + 1]; h_vel3[3 * (size_t)i + 2] = v4[4 * (size_t)i + 2]; }
