@@ -134,8 +134,10 @@ void nbody_release_cached(void);
 const char* nbody_last_error(void);
 /* Kernel launches issued by this library in this process (all contexts). */
 long long nbody_launch_count(void);
-/* Describes variant `id` (1..count) into buf; returns the number of variants. */
+/* Describes variant `id` into buf (empty string for an unknown id); returns the
+ * number of variants.  nbody_variant_id(i), i = 0..count-1, lists the ids. */
 int nbody_variant_info(int id, char* buf, size_t buflen);
+int nbody_variant_id(int index);
 /* Variant / grid actually used by ctx (after AUTO resolution). */
 int nbody_ctx_info(nbody_ctx* ctx, int* variant, int* grid_ctas, int* ctas_per_sm, int* sm_count);
 

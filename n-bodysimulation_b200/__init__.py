@@ -63,6 +63,7 @@ SIGNATURES = {
     "nbody_last_error": (C.c_char_p, []),
     "nbody_launch_count": (C.c_longlong, []),
     "nbody_variant_info": (C.c_int, [C.c_int, C.c_char_p, C.c_size_t]),
+    "nbody_variant_id": (C.c_int, [C.c_int]),
     "nbody_ctx_info": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "nbody_ic_uniform": (C.c_int, [_vp, C.c_int, C.c_ulonglong, C.c_float, C.c_float, C.c_float]),
     "nbody_ic_plummer": (C.c_int, [_vp, _vp, C.c_int, C.c_ulonglong]),
@@ -98,11 +99,12 @@ def launch_count() -> int:
 
 
 def variants() -> dict:
-    buf = C.create_string_buffer(256)
-    n = lib.nbody_variant_info(1, buf, 256)
+    buf = C.create_string_buffer(320)
+    n = lib.nbody_variant_info(1, buf, 320)
     out = {}
-    for i in range(1, n + 1):
-        lib.nbody_variant_info(i, buf, 256)
+    for k in range(n):
+        i = lib.nbody_variant_id(k)
+        lib.nbody_variant_info(i, buf, 320)
         out[i] = buf.value.decode()
     return out
 

@@ -49,13 +49,17 @@ struct Variant {
     int id;
     const char* name;
     int T, NT, UJ, unroll, packed, minb;
+    int cs, cmode;   // cluster size (1 = none); 1 = TMA multicast of source units, 2 = j-split + DSMEM reduction
     void (*kernel)(const ForceArgs);
-    size_t smem() const { return (size_t)kStages * UJ * 16 + 16 * kStages + 16; }
+    size_t smem() const { return (size_t)kStages * UJ * 16 + 16 * kStages + 16 + (cmode == 2 ? (size_t)TI() * 16 : 0); }
     int TI() const { return T * NT; }
+    int TS() const { return cmode == 1 ? TI() * cs : TI(); }          // targets per worker tile
 };
 
 #define VARIANT(id, T, NT, UJ, UN, PK, MB) \
-    { id, "T" #T "_NT" #NT "_UJ" #UJ "_U" #UN "_" #PK "_B" #MB, T, NT, UJ, UN, PK, MB, force_kernel<T, NT, UJ, UN, PK, MB> }
+    { id, "T" #T "_NT" #NT "_UJ" #UJ "_U" #UN "_" #PK "_B" #MB, T, NT, UJ, UN, PK, MB, 1, 0, force_kernel<T, NT, UJ, UN, PK, MB> }
+#define CVARIANT(id, T, NT, UJ, UN, PK, MB, CS, CM) \
+    { id, "T" #T "_NT" #NT "_UJ" #UJ "_U" #UN "_" #PK "_B" #MB "_C" #CS "m" #CM, T, NT, UJ, UN, PK, MB, CS, CM, force_kernel<T, NT, UJ, UN, PK, MB, CS, CM> }
 
 // packed = FFMA2 path, 0 = scalar FFMA path (kept for the with/without evidence)
 const Variant kVariants[] = {
@@ -104,6 +108,25 @@ const Variant kVariants[] = {
     VARIANT(43, 10, 256, 256, 1, 1, 1),
     VARIANT(44, 8, 256, 512, 2, 1, 1),
     VARIANT(45, 6, 256, 256, 2, 1, 1),
+    VARIANT(46, 6, 256, 256, 2, 4, 1),
+    VARIANT(47, 6, 256, 256, 4, 4, 1),
+    VARIANT(48, 6, 256, 256, 4, 1, 1),
+    VARIANT(49, 8, 256, 256, 2, 4, 1),
+    VARIANT(50, 6, 256, 512, 2, 4, 1),
+    VARIANT(51, 4, 256, 256, 4, 4, 2),
+    VARIANT(52, 6, 256, 256, 1, 4, 1),
+    // thread-block-cluster variants: m1 = TMA multicast, m2 = j-split with DSMEM reduction
+    CVARIANT(60, 6, 256, 256, 2, 1, 1, 2, 1),
+    CVARIANT(61, 6, 256, 256, 2, 1, 1, 4, 1),
+    CVARIANT(62, 6, 256, 512, 2, 1, 1, 2, 1),
+    CVARIANT(63, 4, 256, 256, 4, 1, 2, 2, 1),
+    CVARIANT(64, 6, 256, 256, 2, 1, 1, 2, 2),
+    CVARIANT(65, 6, 256, 256, 2, 1, 1, 4, 2),
+    CVARIANT(66, 2, 256, 256, 8, 1, 3, 2, 2),
+    CVARIANT(67, 2, 256, 256, 8, 1, 3, 4, 2),
+    CVARIANT(68, 1, 128, 64, 8, 1, 8, 4, 2),
+    CVARIANT(69, 2, 128, 128, 8, 1, 6, 8, 2),
+    CVARIANT(70, 6, 256, 256, 2, 1, 1, 8, 2),
 };
 const int kNumVariants = (int)(sizeof kVariants / sizeof kVariants[0]);
 constexpr int kSlotAlign = 1024;   // bodies; multiple of every variant's UJ
@@ -118,16 +141,18 @@ const Variant* find_variant(int id)
 int auto_variant(int n_targets, int n_sources)
 {
     (void)n_sources;
-    if (n_targets >= 65536) return 45;   // T6 x 256 threads, 1 CTA/SM: best of the r1 sweeps (profiles/)
-    if (n_targets >= 8192) return 13;
-    return 12;
+    // best of the r1 sweeps (profiles/r1_variant_sweep_*.jsonl); the cluster variants (60-70)
+    // measured neutral (C2 multicast) or slower (C4/C8, DSMEM j-split) and are opt-in only
+    if (n_targets >= 12288) return 45;   // T6 x 256 threads, 1 CTA/SM
+    if (n_targets >= 2048) return 3;     // T2 x 256 threads, 3 CTAs/SM
+    return 12;                           // T1 x 128 threads, 64-body units
 }
 
 int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
 // ---- launch plan for one (variant, targets, J) ---------------------------------------------------
 struct Plan {
-    int grid = 0, occ = 0, maxseg = 0, num_itiles = 0;
+    int grid = 0, occ = 0, maxseg = 0, num_itiles = 0, num_counters = 0;
     size_t partial_bytes = 0;
 };
 
@@ -137,15 +162,29 @@ int make_plan(const Variant* v, int sm_count, int grid_override, int n_targets, 
     CU(cudaFuncSetAttribute(v->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v->smem()));
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pl.occ, v->kernel, v->NT, v->smem()));
     if (pl.occ < 1) return fail(NBODY_E_CUDA, "variant %s does not fit on an SM", v->name);
-    pl.num_itiles = (n_targets + v->TI() - 1) / v->TI();
+    long long workers = (long long)sm_count * pl.occ;   // CTAs, or clusters for the cluster variants
+    if (v->cs > 1) {
+        cudaLaunchConfig_t cfg = {};
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = v->cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.gridDim = dim3((unsigned)(sm_count * pl.occ / v->cs * v->cs)); cfg.blockDim = dim3(v->NT);
+        cfg.dynamicSmemBytes = v->smem(); cfg.attrs = at; cfg.numAttrs = 1;
+        int ncl = 0;
+        CU(cudaOccupancyMaxActiveClusters(&ncl, v->kernel, &cfg));
+        if (ncl < 1) return fail(NBODY_E_CUDA, "no cluster of %d CTAs of variant %s can be resident", v->cs, v->name);
+        workers = ncl;
+    }
+    pl.num_itiles = (n_targets + v->TS() - 1) / v->TS();
     const unsigned long long U = (unsigned long long)pl.num_itiles * (unsigned long long)J;
-    long long grid = grid_override > 0 ? grid_override : (long long)sm_count * pl.occ;
-    if ((unsigned long long)grid > U) grid = (long long)U;
-    if (grid < 1) grid = 1;
-    pl.grid = (int)grid;
-    const unsigned long long q = U / (unsigned long long)grid;   // smallest range, >= 1 when U > 0
+    if (grid_override > 0) workers = v->cs > 1 ? (grid_override / v->cs > 0 ? grid_override / v->cs : 1) : grid_override;
+    if ((unsigned long long)workers > U) workers = (long long)U;
+    if (workers < 1) workers = 1;
+    pl.grid = (int)workers * v->cs;
+    const unsigned long long q = U / (unsigned long long)workers;   // smallest range, >= 1 when U > 0
     pl.maxseg = q > 0 ? (int)((unsigned long long)(J - 1) / q) + 2 : 2;
-    pl.partial_bytes = (size_t)pl.num_itiles * pl.maxseg * v->TI() * sizeof(float4);
+    pl.num_counters = pl.num_itiles * v->cs;
+    pl.partial_bytes = (size_t)pl.num_itiles * (v->cmode == 1 ? v->cs : 1) * pl.maxseg * v->TI() * sizeof(float4);
     *out = pl;
     return NBODY_OK;
 }
@@ -155,7 +194,17 @@ int launch_force(const Variant* v, const Plan& pl, const ForceArgs& args_in, cud
     ForceArgs args = args_in;
     args.k_one = 1.0f;
     args.k_negzero = -0.0f;
-    v->kernel<<<pl.grid, v->NT, v->smem(), st>>>(args);
+    if (v->cs > 1) {
+        cudaLaunchConfig_t cfg = {};
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = v->cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.gridDim = dim3(pl.grid); cfg.blockDim = dim3(v->NT); cfg.dynamicSmemBytes = v->smem(); cfg.stream = st;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        CU(cudaLaunchKernelEx(&cfg, v->kernel, args));
+    } else {
+        v->kernel<<<pl.grid, v->NT, v->smem(), st>>>(args);
+    }
     g_launches.fetch_add(1, std::memory_order_relaxed);
     CU(cudaGetLastError());
     return NBODY_OK;
@@ -242,10 +291,21 @@ int nbody_params_default(nbody_params* p)
 int nbody_variant_info(int id, char* buf, size_t buflen)
 {
     const Variant* v = find_variant(id);
-    if (v && buf && buflen)
-        snprintf(buf, buflen, "%s: %d targets/thread, %d threads/CTA, %d sources/tile, unroll %d pairs, %s FP32, min %d CTAs/SM, %zu B smem",
-                 v->name, v->T, v->NT, v->UJ, v->unroll, v->packed == 0 ? "scalar" : v->packed == 1 ? "packed f32x2" : v->packed == 2 ? "packed f32x2 (all FFMA2)" : "packed f32x2 + prefetch", v->minb, v->smem());
+    if (buf && buflen) buf[0] = 0;
+    if (v && buf && buflen) {
+        char cl[96] = "";
+        if (v->cs > 1) snprintf(cl, sizeof cl, ", clusters of %d CTAs (%s)", v->cs, v->cmode == 1 ? "TMA multicast of source units" : "j-split, DSMEM reduction");
+        snprintf(buf, buflen, "%s: %d targets/thread, %d threads/CTA, %d sources/tile, unroll %d pairs, %s FP32, min %d CTAs/SM, %zu B smem%s",
+                 v->name, v->T, v->NT, v->UJ, v->unroll,
+                 v->packed == 0 ? "scalar" : v->packed == 1 ? "packed f32x2" : v->packed == 2 ? "packed f32x2 (all FFMA2)" : v->packed == 3 ? "packed f32x2 + prefetch" : "packed f32x2 + first-pair prefetch",
+                 v->minb, v->smem(), cl);
+    }
     return kNumVariants;
+}
+
+int nbody_variant_id(int index)
+{
+    return index >= 0 && index < kNumVariants ? kVariants[index].id : 0;
 }
 
 size_t nbody_shard_slot_bytes(int n_bodies, int world)
@@ -326,12 +386,12 @@ int nbody_create(nbody_ctx** out, const nbody_params* p)
     TRYCU(cudaMalloc(&c->packed[0], sb));
     TRYCU(cudaMalloc(&c->packed[1], sb));
     TRYCU(cudaMalloc(&c->partial, partial_bytes));
-    TRYCU(cudaMalloc(&c->counters, (size_t)c->plan_full.num_itiles * sizeof(unsigned)));
+    TRYCU(cudaMalloc(&c->counters, (size_t)c->plan_full.num_counters * sizeof(unsigned)));
     TRYCU(cudaMemset(c->V, 0, tb));
     TRYCU(cudaMemset(c->A, 0, tb));
     TRYCU(cudaMemset(c->packed[0], 0, sb));
     TRYCU(cudaMemset(c->packed[1], 0, sb));
-    TRYCU(cudaMemset(c->counters, 0, (size_t)c->plan_full.num_itiles * sizeof(unsigned)));
+    TRYCU(cudaMemset(c->counters, 0, (size_t)c->plan_full.num_counters * sizeof(unsigned)));
     TRYCU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     TRYCU(cudaEventCreate(&c->ev0));
     TRYCU(cudaEventCreate(&c->ev1));

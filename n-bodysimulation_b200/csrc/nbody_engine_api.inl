@@ -211,8 +211,8 @@ int get_cached(int n, bool host_buffers, Cached** out)
         if (rc) { k = Cached(); return rc; }
         cudaError_t e = cudaMalloc(&k.packed, (size_t)k.n_pad * sizeof(float4));
         if (e == cudaSuccess) e = cudaMalloc(&k.partial, k.plan.partial_bytes);
-        if (e == cudaSuccess) e = cudaMalloc(&k.counters, (size_t)k.plan.num_itiles * sizeof(unsigned));
-        if (e == cudaSuccess) e = cudaMemset(k.counters, 0, (size_t)k.plan.num_itiles * sizeof(unsigned));
+        if (e == cudaSuccess) e = cudaMalloc(&k.counters, (size_t)k.plan.num_counters * sizeof(unsigned));
+        if (e == cudaSuccess) e = cudaMemset(k.counters, 0, (size_t)k.plan.num_counters * sizeof(unsigned));
         if (e != cudaSuccess) { free_cached(k); return fail(NBODY_E_CUDA, "scratch allocation failed: %s", cudaGetErrorString(e)); }
     }
     if (host_buffers && !k.X) {

@@ -111,52 +111,88 @@ __device__ __forceinline__ int unit_owner(u64 u, u64 U, u64 W) { return (int)(((
 
 // MODE: 0 scalar FFMA | 1 packed FADD2/FMUL2/FFMA2 | 2 packed, every op issued as FFMA2
 //       (x*1+y, x*y-0: bit-identical results) | 3 packed + source pairs prefetched one group ahead
-template <int T, int NT, int UJ, int UNROLL, int MODE, int MINB>
+//       | 4 packed + only the next group's FIRST pair prefetched
+// CS / CMODE: thread-block clusters (launch attribute clusterDim = CS).
+//   CMODE 1 "multicast": the CS CTAs of a cluster own CS neighbouring target tiles and stream
+//           the SAME source units; CTA r fetches slice r of each unit and TMA-multicasts it
+//           into every CTA's ring, so one L2/HBM read feeds CS SMs.  The stream-K cut is made
+//           between clusters.
+//   CMODE 2 "j-split": the CS CTAs share ONE target tile and take every CS-th source unit of
+//           the segment; the partial sums are combined through distributed shared memory
+//           (ld.shared::cluster, fixed rank order), CTA r finishing slice r of the tile.
+template <int T, int NT, int UJ, int UNROLL, int MODE, int MINB, int CS = 1, int CMODE = 0>
 __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
 {
     constexpr bool PACKED = MODE != 0;
+    constexpr bool MCAST = CS > 1 && CMODE == 1;
+    constexpr bool JSPLIT = CS > 1 && CMODE == 2;
     constexpr int TI = T * NT;
+    constexpr int TS = MCAST ? TI * CS : TI;   // targets of one worker's tile
     constexpr uint32_t kStageBytes = UJ * 16;
     static_assert((kStages & (kStages - 1)) == 0, "ring depth must be a power of two");
     static_assert((UJ / 2) % UNROLL == 0, "unroll must divide the pairs per unit");
+    static_assert(CS == 1 || CMODE == 1 || CMODE == 2, "cluster variants need a mode");
+    static_assert(!MCAST || (kStageBytes / CS) % 16 == 0, "multicast slices must be 16-byte multiples");
+    static_assert(!JSPLIT || (TI / CS) % 32 == 0, "j-split slices must be whole warps");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const uint32_t smem_base = smem_u32(smem_raw);
     const uint32_t bar_full = smem_base + kStages * kStageBytes;
     const uint32_t bar_empty = bar_full + 8 * kStages;
     volatile int* s_flag = reinterpret_cast<volatile int*>(smem_raw + kStages * kStageBytes + 16 * kStages);
+    float4* s_red = reinterpret_cast<float4*>(smem_raw + kStages * kStageBytes + 16 * kStages + 16);   // JSPLIT only: [TI]
 
     const int tid = threadIdx.x, lane = tid & 31;
+    const uint32_t crank = CS > 1 ? cluster_ctarank() : 0u;
     const int J = a.ra_count + a.rb_count;
-    const int num_itiles = (a.n_targets + TI - 1) / TI;
+    const int num_itiles = (a.n_targets + TS - 1) / TS;
     const u64 U = (u64)num_itiles * (u64)J;
-    const u64 W = gridDim.x, w = blockIdx.x;
+    const u64 W = gridDim.x / CS, w = blockIdx.x / CS;   // workers = clusters
     const u64 u_begin = w * U / W, u_end = (w + 1) * U / W;
-    const int n_fetch = (int)(u_end - u_begin);
 
     if (tid == 0) {
 #pragma unroll
         for (int s = 0; s < kStages; ++s) {
             mbar_init(bar_full + 8 * s, 1);
-            mbar_init(bar_empty + 8 * s, NT / 32);
+            mbar_init(bar_empty + 8 * s, MCAST ? CS * (NT / 32) : NT / 32);
         }
         mbar_fence_init();
     }
-    __syncthreads();
+    if (CS > 1) cluster_sync_all();   // peers' barriers exist before any multicast / remote arrive
+    else __syncthreads();
 
     // ---- producer state (thread 0 only) ------------------------------------------------
-    int pj = (int)(u_begin % (u64)J);   // next source unit (index into A|B) to fetch
+    // JSPLIT: within each segment (part of one tile's unit row inside [u_begin, u_end)) this
+    // CTA takes the units at offset crank, crank+CS, ... from the segment start.
+    u64 pu = u_begin;                   // next linear unit to consider
     int kf = 0;                         // fetches issued so far
-    auto issue = [&]() {
+    auto issue = [&]() -> bool {
+        if (JSPLIT) {
+            while (pu < u_end) {
+                u64 seg0 = (pu / (u64)J) * (u64)J;
+                if (seg0 < u_begin) seg0 = u_begin;
+                if ((pu - seg0) % CS == crank) break;
+                ++pu;
+            }
+        }
+        if (pu >= u_end) return false;
+        const int pj = (int)(pu % (u64)J);
         const int s = kf & (kStages - 1), n = kf / kStages;
         if (n > 0) mbar_wait(bar_empty + 8 * s, (n - 1) & 1);
         const int ju = pj < a.ra_count ? a.ra_begin + pj : a.rb_begin + (pj - a.ra_count);
         mbar_arrive_expect_tx(bar_full + 8 * s, kStageBytes);
-        tma_bulk_g2s(smem_base + s * kStageBytes, a.src + (size_t)ju * UJ, kStageBytes, bar_full + 8 * s);
-        if (++pj == J) pj = 0;
+        if (MCAST) {
+            constexpr uint32_t kSlice = kStageBytes / CS;
+            tma_bulk_g2s_mcast(smem_base + s * kStageBytes + crank * kSlice, reinterpret_cast<const unsigned char*>(a.src + (size_t)ju * UJ) + crank * kSlice,
+                               kSlice, bar_full + 8 * s, (uint16_t)((1u << CS) - 1u));
+        } else {
+            tma_bulk_g2s(smem_base + s * kStageBytes, a.src + (size_t)ju * UJ, kStageBytes, bar_full + 8 * s);
+        }
+        ++pu;
         ++kf;
+        return true;
     };
     if (tid == 0)
-        while (kf < kLookahead && kf < n_fetch) issue();
+        while (kf < kLookahead && issue()) {}
 
     const u64 eps2p = pack2(a.eps2, a.eps2);
     int k = 0;   // units consumed so far
@@ -172,7 +208,7 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
         float sx[T], sy[T], sz[T], qx[T], qy[T], qz[T];   // scalar variant
 #pragma unroll
         for (int t = 0; t < T; ++t) {
-            const int gi = it * TI + tid + t * NT;
+            const int gi = (MCAST ? it * CS + (int)crank : it) * TI + tid + t * NT;
             float4 xi = make_float4(0.f, 0.f, 0.f, 0.f);
             if (gi < a.n_targets) xi = a.X[gi];
             if (PACKED) {
@@ -186,8 +222,8 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
 
         // ---- stream the source units of this segment ------------------------------------
 #pragma unroll 1
-        for (int jj = 0; jj < jn; ++jj, ++k) {
-            if (tid == 0 && kf < n_fetch) issue();
+        for (int jj = JSPLIT ? (int)crank : 0; jj < jn; jj += JSPLIT ? CS : 1, ++k) {
+            if (tid == 0) issue();
             const int s = k & (kStages - 1);
             mbar_wait(bar_full + 8 * s, (k / kStages) & 1);
             const ulonglong2* sp = reinterpret_cast<const ulonglong2*>(smem_raw + s * kStageBytes);
@@ -228,6 +264,20 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
 #pragma unroll
                     for (int q = 0; q < UNROLL; ++q) { cxy[q] = nxy[q]; czm[q] = nzm[q]; }
                 }
+            } else if (MODE == 4) {
+                // first pair of the NEXT group is loaded while this group is computed, so no
+                // LDS latency is exposed at the loop top (r1 source-page profile: 26 of 646
+                // cycles per iteration were short-scoreboard stalls on that load).  The last
+                // group reads 32 B past the stage (next stage / barrier words): discarded.
+                ulonglong2 cxy = sp[0], czm = sp[1];
+#pragma unroll 1
+                for (int p = 0; p < UJ / 2; p += UNROLL) {
+                    const ulonglong2 nxy = sp[2 * (p + UNROLL)], nzm = sp[2 * (p + UNROLL) + 1];
+                    interact2(cxy, czm);
+#pragma unroll
+                    for (int q = 1; q < UNROLL; ++q) interact2(sp[2 * (p + q)], sp[2 * (p + q) + 1]);
+                    cxy = nxy; czm = nzm;
+                }
             } else {
 #pragma unroll 1
             for (int p = 0; p < UJ / 2; p += UNROLL) {
@@ -259,7 +309,11 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
             }
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(bar_empty + 8 * s);
+            if (MCAST) {   // every producer of the cluster writes this stage: release it in all CTAs
+                if (lane < CS) mbar_arrive_cluster(mapa_shared(bar_empty + 8 * s, (uint32_t)lane));
+            } else if (lane == 0) {
+                mbar_arrive(bar_empty + 8 * s);
+            }
         }
 
         // ---- segment done: fused epilogue, or split-tile fix-up ------------------------
@@ -275,46 +329,116 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
                 fx[t] = qx[t]; fy[t] = qy[t]; fz[t] = qz[t];
             }
         }
-        bool finish = true;
-        if (!(j0 == 0 && jn == J)) {
+        const bool split = !(j0 == 0 && jn == J);
+        int w_first = 0, nseg = 1;
+        if (split) {
             const u64 first_u = (u64)it * (u64)J;
-            const int w_first = unit_owner(first_u, U, W);
-            const int nseg = unit_owner(first_u + (u64)J - 1, U, W) - w_first + 1;
-            float4* tile_part = a.partial + (size_t)it * a.maxseg * TI;
-            float4* slot = tile_part + (size_t)((int)w - w_first) * TI;
+            w_first = unit_owner(first_u, U, W);
+            nseg = unit_owner(first_u + (u64)J - 1, U, W) - w_first + 1;
+        }
+        if (!JSPLIT) {
+            const int vt = MCAST ? it * CS + (int)crank : it;   // tile whose T*NT targets this CTA holds
+            bool finish = true;
+            if (split) {
+                float4* tile_part = a.partial + (size_t)vt * a.maxseg * TI;
+                float4* slot = tile_part + (size_t)((int)w - w_first) * TI;
 #pragma unroll
-            for (int t = 0; t < T; ++t) slot[tid + t * NT] = make_float4(fx[t], fy[t], fz[t], 0.f);
-            __threadfence();
-            __syncthreads();
-            if (tid == 0) {
-                const unsigned old = atomicAdd(&a.counters[it], 1u);
-                *s_flag = (old == (unsigned)(nseg - 1));
-            }
-            __syncthreads();
-            finish = (*s_flag != 0);
-            if (finish) {
+                for (int t = 0; t < T; ++t) slot[tid + t * NT] = make_float4(fx[t], fy[t], fz[t], 0.f);
                 __threadfence();
+                __syncthreads();
+                if (tid == 0) {
+                    const unsigned old = atomicAdd(&a.counters[vt], 1u);
+                    *s_flag = (old == (unsigned)(nseg - 1));
+                }
+                __syncthreads();
+                finish = (*s_flag != 0);
+                if (finish) {
+                    __threadfence();
 #pragma unroll
-                for (int t = 0; t < T; ++t) { fx[t] = 0.f; fy[t] = 0.f; fz[t] = 0.f; }
-                for (int sg = 0; sg < nseg; ++sg) {
+                    for (int t = 0; t < T; ++t) { fx[t] = 0.f; fy[t] = 0.f; fz[t] = 0.f; }
+                    for (int sg = 0; sg < nseg; ++sg) {
 #pragma unroll
-                    for (int t = 0; t < T; ++t) {
-                        const float4 p = __ldcg(tile_part + (size_t)sg * TI + tid + t * NT);
-                        fx[t] = __fadd_rn(fx[t], p.x); fy[t] = __fadd_rn(fy[t], p.y); fz[t] = __fadd_rn(fz[t], p.z);
+                        for (int t = 0; t < T; ++t) {
+                            const float4 p = __ldcg(tile_part + (size_t)sg * TI + tid + t * NT);
+                            fx[t] = __fadd_rn(fx[t], p.x); fy[t] = __fadd_rn(fy[t], p.y); fz[t] = __fadd_rn(fz[t], p.z);
+                        }
+                    }
+                    if (tid == 0) a.counters[vt] = 0u;
+                }
+            }
+            if (finish) {
+#pragma unroll
+                for (int t = 0; t < T; ++t) {
+                    const int gi = vt * TI + tid + t * NT;
+                    integrate_one(a, gi, gi < a.n_targets, fx[t], fy[t], fz[t], lane);
+                }
+            }
+        } else {
+            // ---- j-split: combine the CS partial sums through distributed shared memory ----
+            constexpr int SL = TI / CS;                 // targets finished by each CTA
+            constexpr int RT = (SL + NT - 1) / NT;
+#pragma unroll
+            for (int t = 0; t < T; ++t) s_red[tid + t * NT] = make_float4(fx[t], fy[t], fz[t], 0.f);
+            cluster_sync_all();
+            float rx[RT], ry[RT], rz[RT];
+            const uint32_t red_mine = smem_u32(s_red) + (uint32_t)(crank * SL) * 16u;
+#pragma unroll
+            for (int i = 0; i < RT; ++i) {
+                rx[i] = 0.f; ry[i] = 0.f; rz[i] = 0.f;
+                const int kk = tid + i * NT;
+                if (kk < SL) {
+#pragma unroll
+                    for (int q = 0; q < CS; ++q) {   // fixed rank order: deterministic
+                        const float4 p = ld_dsmem_f4(mapa_shared(red_mine + (uint32_t)kk * 16u, (uint32_t)q));
+                        rx[i] = __fadd_rn(rx[i], p.x); ry[i] = __fadd_rn(ry[i], p.y); rz[i] = __fadd_rn(rz[i], p.z);
                     }
                 }
-                if (tid == 0) a.counters[it] = 0u;
             }
-        }
-        if (finish) {
+            cluster_sync_all();   // every peer has read this CTA's sums: s_red may be reused
+            bool finish = true;
+            if (split) {
+                float4* tile_part = a.partial + (size_t)it * a.maxseg * TI + (size_t)crank * SL;
+                float4* slot = tile_part + (size_t)((int)w - w_first) * TI;
 #pragma unroll
-            for (int t = 0; t < T; ++t) {
-                const int gi = it * TI + tid + t * NT;
-                integrate_one(a, gi, gi < a.n_targets, fx[t], fy[t], fz[t], lane);
+                for (int i = 0; i < RT; ++i)
+                    if (tid + i * NT < SL) slot[tid + i * NT] = make_float4(rx[i], ry[i], rz[i], 0.f);
+                __threadfence();
+                __syncthreads();
+                if (tid == 0) {
+                    const unsigned old = atomicAdd(&a.counters[it * CS + (int)crank], 1u);
+                    *s_flag = (old == (unsigned)(nseg - 1));
+                }
+                __syncthreads();
+                finish = (*s_flag != 0);
+                if (finish) {
+                    __threadfence();
+#pragma unroll
+                    for (int i = 0; i < RT; ++i) { rx[i] = 0.f; ry[i] = 0.f; rz[i] = 0.f; }
+                    for (int sg = 0; sg < nseg; ++sg) {
+#pragma unroll
+                        for (int i = 0; i < RT; ++i) {
+                            if (tid + i * NT < SL) {
+                                const float4 p = __ldcg(tile_part + (size_t)sg * TI + tid + i * NT);
+                                rx[i] = __fadd_rn(rx[i], p.x); ry[i] = __fadd_rn(ry[i], p.y); rz[i] = __fadd_rn(rz[i], p.z);
+                            }
+                        }
+                    }
+                    if (tid == 0) a.counters[it * CS + (int)crank] = 0u;
+                }
+            }
+            if (finish) {
+#pragma unroll
+                for (int i = 0; i < RT; ++i) {
+                    if (tid + i * NT < SL) {   // warp-uniform: SL and NT are multiples of 32
+                        const int gi = it * TI + (int)crank * SL + tid + i * NT;
+                        integrate_one(a, gi, gi < a.n_targets, rx[i], ry[i], rz[i], lane);
+                    }
+                }
             }
         }
         u += (u64)jn;
     }
+    if (CS > 1) cluster_sync_all();   // no CTA leaves while peers may still touch its shared memory
 }
 
 // ---- AoS float4 -> packed pair layout (pre-pass of the in-place API and of upload) ----
