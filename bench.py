@@ -2,7 +2,7 @@
 """bench.py -- headline benchmark of the B200 all-pairs N-body step.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
-                    [--n BODIES] [--ic uniform|plummer] [--variant ID]
+                    [--bodies BODIES] [--ic uniform|plummer] [--variant ID]
 
 Metric (BASELINE.json): Giga body-interactions/s, device-timed, plus the fraction
 of B200 FP32 peak at 20 FLOP/interaction.  A step = one full all-pairs step
@@ -38,7 +38,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=1 << 20)
+    ap.add_argument("--bodies", "--n", dest="n", type=int, default=1 << 20)   # torchrun swallows a bare --n: use --bodies there
     ap.add_argument("--ic", default="uniform", choices=["uniform", "plummer"])
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
