@@ -30,9 +30,20 @@ void simulate(float4* bodies, float3* accelerations, float3* velocity, int N);
 /*
  * TestProject/kernel.cuh:3-7 (simulateVisual, simulateVisual_embParallel and its
  * _float3 / _fadl / _fadl4 forms) take a cudaGraphicsResource* that only an
- * OpenGL context can produce.  There is no graphics stack on this box, so they
- * are not part of this library ("unavailable on this box").
+ * OpenGL context can produce: "unavailable on this box" (DESIGN.md).  Their
+ * HEADLESS forms below keep every other argument and take the device pointer
+ * the reference obtains from cudaGraphicsResourceGetMappedPointer
+ * (kernel.cu:476-480) directly.  d_reduceMatrix (the reference's O(N^2/32)
+ * scratch, main.cpp:257-269) is accepted and ignored -- it may be null: the
+ * engine's split of the source range between CTAs keeps its partial sums in
+ * O(N) scratch of its own.  Integrator as the reduction flavours write it
+ * (kernel.cu:455-463: half-kick in double).
  */
+void simulateHeadless(float4* d_bodies, float4* d_accelerations, float4* d_velocity, int N);
+void simulateHeadless_embParallel(float4* d_bodies, float4* d_accelerations, float4* d_velocity, float4* d_reduceMatrix, int N);
+void simulateHeadless_embParallel_float3(float4* d_bodies, float3* d_accelerations, float3* d_velocity, float3* d_reduceMatrix, int N);
+void simulateHeadless_embParallel_fadl(float4* d_bodies, float4* d_accelerations, float4* d_velocity, float4* d_reduceMatrix, int N);
+void simulateHeadless_embParallel_fadl4(float4* d_bodies, float4* d_accelerations, float4* d_velocity, float4* d_reduceMatrix, int N);
 
 /* Run-time replacements for the compile-time EPS2 / DT the reference bakes into
  * its kernel; they affect the float4 overload above.  Defaults: EPS2, DT. */

@@ -34,6 +34,8 @@ extern "C" {
 /* integrator arithmetic */
 #define NBODY_INTEG_F32   0   /* TestProject/kernel.cu:116-124: float, 0.5f*DT            */
 #define NBODY_INTEG_F64   1   /* Sim-Without-OpenGL-Integration/kernel.cu:71-77: double   */
+#define NBODY_INTEG_MIXED 2   /* TestProject/kernel.cu:455-463 (reduction flavours):      */
+                              /* `0.5 * DT * a` in double, drift `DT * v` in float (FMA)  */
 
 /* kernel variant: 0 = choose from N; others are listed by nbody_variant_info() */
 #define NBODY_VARIANT_AUTO 0
@@ -127,8 +129,54 @@ int nbody_step_inplace_f4(float* d_bodies4, float* d_accel4, float* d_vel4, int 
  * As in the reference, accelerations are not returned (it zeroes them). */
 int nbody_step_host_f3(float* h_bodies4, float* h_accel3, float* h_vel3, int n, double eps2, double dt);
 
-/* Releases the per-(device, N) scratch the two calls above keep between calls. */
+/* One in-place step on DEVICE arrays with every compile-time switch of the
+ * reference (TestProject/constants.h:4-7 REDUCTION / FLOAT_3 / FADL) as a
+ * run-time option.  This is what the headless forms of the reduction-variant
+ * launchers (TestProject/kernel.cuh:4-7, see include/kernel.cuh) forward to. */
+typedef struct nbody_step_opts {
+    float eps2, dt;      /* [EPS2, DT]                                                     */
+    int   integrator;    /* NBODY_INTEG_F32 | NBODY_INTEG_MIXED                            */
+    int   va_float3;     /* 1: d_accel / d_vel are float3[N] (FLOAT_3 1, main.cpp:233-269,  */
+                         /*    kernel.cu:439-469); 0: float4[N]                            */
+    int   variant;       /* kernel variant, NBODY_VARIANT_AUTO = pick from N               */
+} nbody_step_opts;
+int nbody_step_opts_default(nbody_step_opts* o);
+int nbody_step_inplace_opts(float* d_bodies4, void* d_accel, void* d_vel, int n, const nbody_step_opts* o);
+
+/* Releases the per-(device, N) scratch the calls above keep between calls. */
 void nbody_release_cached(void);
+
+/* ---- headless frame: the reference's per-step OpenGL draw as CUDA --------
+ * Shader arithmetic of TestProject/simulation_visualization.cpp:15-56 (weight,
+ * NDC position, mix(green, red, weight)), 1-pixel points with the depth test
+ * of :132-135, window 800x600 (simulation_visualization.h:8-9), cleared every
+ * frame (main.cpp:48).  The GL/GLFW path itself is unavailable on this box;
+ * the frame is a device RGBA8 buffer, rows top-down, 4*width*height bytes. */
+typedef struct nbody_view {
+    int   width, height;         /* [800, 600]  WINDOW_WIDTH / WINDOW_HEIGHT                  */
+    float max_x, max_y, max_z;   /* [200000]    MAX_VIEWX/Y/Z, constants.h:21-23 (uniforms)   */
+    float min_w, max_w;          /* [1e5, 1e9]  MIN_W / MAX_W, constants.h:18-19 (uniforms)   */
+    int   depth_test;            /* [1] GL_LESS; 0 = off (the last body drawn wins a pixel)   */
+} nbody_view;
+int nbody_view_default(nbody_view* v);
+/* DEVICE float4 positions in, DEVICE RGBA8 frame out; synchronous, current device.
+ * Replaces renderBodies (simulation_visualization.cpp:165-169) + both shaders. */
+int nbody_render_device(const float* d_bodies4, int n, const nbody_view* v, unsigned char* d_rgba);
+/* Frame of the context's current positions into a HOST buffer (unsharded contexts). */
+int nbody_render(nbody_ctx* ctx, const nbody_view* v, unsigned char* h_rgba);
+/* Writes a host RGBA8 frame as a binary PPM (alpha dropped). */
+int nbody_write_ppm(const char* path, const unsigned char* h_rgba, int width, int height);
+
+/* ---- run records: snapshot / resume ---------------------------------------
+ * The reference drops its results (main.cpp:356-366).  A snapshot is the raw
+ * float4 X and V arrays (main.cpp:250-251) after steps_done steps behind a
+ * 64-byte header (csrc/nbody_records.inl).  load works on sharded contexts too
+ * (every rank reads the file and keeps its slice); save needs an unsharded one. */
+int nbody_snapshot_save(nbody_ctx* ctx, const char* path);
+int nbody_snapshot_load(nbody_ctx* ctx, const char* path);
+int nbody_snapshot_info(const char* path, int* n_bodies, long long* steps_done, float* eps2, float* dt);
+/* Full steps taken since the last upload / snapshot load. */
+int nbody_steps_done(nbody_ctx* ctx, long long* steps);
 
 /* ---- introspection ------------------------------------------------------ */
 const char* nbody_last_error(void);

@@ -27,7 +27,7 @@ if not os.path.exists(LIB_PATH):
 
 lib = C.CDLL(LIB_PATH)
 
-NBODY_INTEG_F32, NBODY_INTEG_F64 = 0, 1
+NBODY_INTEG_F32, NBODY_INTEG_F64, NBODY_INTEG_MIXED = 0, 1, 2
 
 
 class NBodyParams(C.Structure):
@@ -36,6 +36,17 @@ class NBodyParams(C.Structure):
                 ("eps2", C.c_float), ("dt", C.c_float), ("integrator", C.c_int),
                 ("device", C.c_int), ("variant", C.c_int), ("grid_ctas", C.c_int),
                 ("eps2_f64", C.c_double), ("dt_f64", C.c_double)]
+
+
+class NBodyStepOpts(C.Structure):
+    """struct nbody_step_opts: the reference's compile-time switches (constants.h:4-7) at run time."""
+    _fields_ = [("eps2", C.c_float), ("dt", C.c_float), ("integrator", C.c_int), ("va_float3", C.c_int), ("variant", C.c_int)]
+
+
+class NBodyView(C.Structure):
+    """struct nbody_view: window size and shader uniforms of simulation_visualization.cpp:203-207."""
+    _fields_ = [("width", C.c_int), ("height", C.c_int), ("max_x", C.c_float), ("max_y", C.c_float), ("max_z", C.c_float),
+                ("min_w", C.c_float), ("max_w", C.c_float), ("depth_test", C.c_int)]
 
 
 _fp = C.POINTER(C.c_float)
@@ -59,7 +70,17 @@ SIGNATURES = {
     "nbody_shard_slot_bytes": (C.c_size_t, [C.c_int, C.c_int]),
     "nbody_step_inplace_f4": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_float, C.c_float]),
     "nbody_step_host_f3": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_double, C.c_double]),
+    "nbody_step_opts_default": (C.c_int, [C.POINTER(NBodyStepOpts)]),
+    "nbody_step_inplace_opts": (C.c_int, [_vp, _vp, _vp, C.c_int, C.POINTER(NBodyStepOpts)]),
     "nbody_release_cached": (None, []),
+    "nbody_view_default": (C.c_int, [C.POINTER(NBodyView)]),
+    "nbody_render_device": (C.c_int, [_vp, C.c_int, C.POINTER(NBodyView), _vp]),
+    "nbody_render": (C.c_int, [_vp, C.POINTER(NBodyView), _vp]),
+    "nbody_write_ppm": (C.c_int, [C.c_char_p, _vp, C.c_int, C.c_int]),
+    "nbody_snapshot_save": (C.c_int, [_vp, C.c_char_p]),
+    "nbody_snapshot_load": (C.c_int, [_vp, C.c_char_p]),
+    "nbody_snapshot_info": (C.c_int, [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_longlong), C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "nbody_steps_done": (C.c_int, [_vp, C.POINTER(C.c_longlong)]),
     "nbody_last_error": (C.c_char_p, []),
     "nbody_launch_count": (C.c_longlong, []),
     "nbody_variant_info": (C.c_int, [C.c_int, C.c_char_p, C.c_size_t]),
@@ -89,7 +110,7 @@ def _ptr(a) -> int:
     if isinstance(a, int):
         return a
     if isinstance(a, np.ndarray):
-        assert a.dtype == np.float32 and a.flags["C_CONTIGUOUS"], "need contiguous float32"
+        assert a.dtype in (np.float32, np.uint8) and a.flags["C_CONTIGUOUS"], "need a contiguous float32 (or uint8 frame) array"
         return a.ctypes.data
     return a.data_ptr()   # torch tensor
 
@@ -128,6 +149,51 @@ def simulate_host_f3(bodies: np.ndarray, accelerations: np.ndarray, velocity: np
                      eps2: float = 0.002, dt: float = 0.01) -> None:
     """Sim-Without-OpenGL-Integration/kernel.cuh:5 -- HOST float4 bodies, float3 velocity."""
     _check(lib.nbody_step_host_f3(_ptr(bodies), _ptr(accelerations), _ptr(velocity), int(N), eps2, dt))
+
+
+def simulate_opts(d_bodies, d_accelerations, d_velocity, N: int, *, integrator: int = NBODY_INTEG_F32,
+                  va_float3: bool = False, variant: int = 0) -> None:
+    """nbody_step_inplace_opts: the in-place step with the reference's build switches as options"""
+    o = NBodyStepOpts()
+    _check(lib.nbody_step_opts_default(C.byref(o)))
+    o.eps2, o.dt, o.integrator, o.va_float3, o.variant = _eps2, _dt, integrator, int(va_float3), variant
+    _check(lib.nbody_step_inplace_opts(_ptr(d_bodies), _ptr(d_accelerations), _ptr(d_velocity), int(N), C.byref(o)))
+
+
+def simulateHeadless_embParallel(d_bodies, d_accelerations, d_velocity, d_reduceMatrix, N: int) -> None:
+    """headless form of TestProject/kernel.cuh:4 (also _fadl / _fadl4, :6-7): float4 V/A, reduction-flavour integrator"""
+    simulate_opts(d_bodies, d_accelerations, d_velocity, N, integrator=NBODY_INTEG_MIXED)
+
+
+def simulateHeadless_embParallel_float3(d_bodies, d_accelerations, d_velocity, d_reduceMatrix, N: int) -> None:
+    """headless form of TestProject/kernel.cuh:5: float3 V/A device arrays"""
+    simulate_opts(d_bodies, d_accelerations, d_velocity, N, integrator=NBODY_INTEG_MIXED, va_float3=True)
+
+
+# ---- headless frame (simulation_visualization.cpp's shaders as CUDA) ------------------------------
+def default_view(**kw) -> NBodyView:
+    v = NBodyView()
+    _check(lib.nbody_view_default(C.byref(v)))
+    for k, val in kw.items():
+        setattr(v, k, val)
+    return v
+
+
+def render_device(d_bodies, N: int, d_rgba, view: NBodyView | None = None) -> None:
+    """DEVICE float4 positions -> DEVICE uint8 RGBA frame (height, width, 4), rows top-down"""
+    view = view or default_view()
+    _check(lib.nbody_render_device(_ptr(d_bodies), int(N), C.byref(view), _ptr(d_rgba)))
+
+
+def write_ppm(path: str, rgba: np.ndarray) -> None:
+    h, w, _ = rgba.shape
+    _check(lib.nbody_write_ppm(path.encode(), rgba.ctypes.data, w, h))
+
+
+def snapshot_info(path: str) -> dict:
+    n, st, e, d = C.c_int(), C.c_longlong(), C.c_float(), C.c_float()
+    _check(lib.nbody_snapshot_info(path.encode(), C.byref(n), C.byref(st), C.byref(e), C.byref(d)))
+    return {"n_bodies": n.value, "steps_done": st.value, "eps2": e.value, "dt": d.value}
 
 
 # ---- initial conditions -----------------------------------------------------------------
@@ -215,6 +281,26 @@ class Simulation:
         ke, pe = C.c_double(), C.c_double()
         _check(lib.nbody_energy(self._h, C.byref(ke), C.byref(pe)))
         return ke.value, pe.value
+
+    def render(self, view: NBodyView | None = None) -> np.ndarray:
+        """frame of the current positions as a host uint8 array (height, width, 4)"""
+        view = view or default_view()
+        img = np.empty((view.height, view.width, 4), np.uint8)
+        _check(lib.nbody_render(self._h, C.byref(view), img.ctypes.data))
+        return img
+
+    def save(self, path: str) -> "Simulation":
+        _check(lib.nbody_snapshot_save(self._h, path.encode()))
+        return self
+
+    def load(self, path: str) -> "Simulation":
+        _check(lib.nbody_snapshot_load(self._h, path.encode()))
+        return self
+
+    def steps_done(self) -> int:
+        st = C.c_longlong()
+        _check(lib.nbody_steps_done(self._h, C.byref(st)))
+        return st.value
 
     # sharded stepping (one Simulation per rank; the caller owns the exchange)
     def shard_local_async(self, stream: int = 0) -> None:

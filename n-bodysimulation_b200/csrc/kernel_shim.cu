@@ -33,3 +33,40 @@ void simulate(float4* bodies, float3* accelerations, float3* velocity, int N)
                                       reinterpret_cast<float*>(velocity), N, 0.002, 0.01);
     if (rc != NBODY_OK) throw std::runtime_error(std::string("simulate: ") + nbody_last_error());
 }
+
+// ---- headless forms of TestProject/kernel.cuh:3-7 --------------------------------------------
+namespace {
+void step_opts(float4* d_bodies, void* d_acc, void* d_vel, int N, int integrator, int f3)
+{
+    nbody_step_opts o;
+    nbody_step_opts_default(&o);
+    o.eps2 = g_eps2; o.dt = g_dt; o.integrator = integrator; o.va_float3 = f3;
+    const int rc = nbody_step_inplace_opts(reinterpret_cast<float*>(d_bodies), d_acc, d_vel, N, &o);
+    if (rc != NBODY_OK) throw std::runtime_error(std::string("simulate: ") + nbody_last_error());
+}
+}
+
+// simulateVisual (kernel.cu:599-625) runs the same `kernel` as simulate()
+void simulateHeadless(float4* d_bodies, float4* d_accelerations, float4* d_velocity, int N)
+{
+    step_opts(d_bodies, d_accelerations, d_velocity, N, NBODY_INTEG_F32, 0);
+}
+// kernel_reduction + inter_block_reduction (kernel.cu:163-246,406-436; launcher :536-565)
+void simulateHeadless_embParallel(float4* d_bodies, float4* d_accelerations, float4* d_velocity, float4*, int N)
+{
+    step_opts(d_bodies, d_accelerations, d_velocity, N, NBODY_INTEG_MIXED, 0);
+}
+// kernel_reduction_float3 + inter_block_reduction_float3 (kernel.cu:250-318,439-469; launcher :567-595)
+void simulateHeadless_embParallel_float3(float4* d_bodies, float3* d_accelerations, float3* d_velocity, float3*, int N)
+{
+    step_opts(d_bodies, d_accelerations, d_velocity, N, NBODY_INTEG_MIXED, 1);
+}
+// "first add during load" forms (kernel_reduction_fadl, kernel.cu:321-402; launchers :472-534): same arithmetic, other launch shape
+void simulateHeadless_embParallel_fadl(float4* d_bodies, float4* d_accelerations, float4* d_velocity, float4*, int N)
+{
+    step_opts(d_bodies, d_accelerations, d_velocity, N, NBODY_INTEG_MIXED, 0);
+}
+void simulateHeadless_embParallel_fadl4(float4* d_bodies, float4* d_accelerations, float4* d_velocity, float4*, int N)
+{
+    step_opts(d_bodies, d_accelerations, d_velocity, N, NBODY_INTEG_MIXED, 0);
+}

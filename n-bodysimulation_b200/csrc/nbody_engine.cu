@@ -240,6 +240,9 @@ struct nbody_ctx {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timed = false;
+    unsigned char* frame = nullptr;              // nbody_render's device RGBA8 frame
+    size_t frame_bytes = 0;
+    long long steps_done = 0;                    // full steps since the last upload / snapshot load
 };
 
 namespace {
@@ -256,7 +259,7 @@ ForceArgs base_args(nbody_ctx* c)
     a.counters = c->counters;
     a.eps2 = c->p.integrator == NBODY_INTEG_F64 ? (float)c->p.eps2_f64 : c->p.eps2;
     a.dt = c->p.dt;
-    a.integ_f64 = c->p.integrator == NBODY_INTEG_F64;
+    a.integ_f64 = c->p.integrator;   // 0 float, 1 double (headless flavour), 2 mixed (reduction flavours)
     a.dt64 = c->p.dt_f64;
     return a;
 }
@@ -320,7 +323,7 @@ void nbody_destroy(nbody_ctx* c)
     cudaSetDevice(c->p.device);
     cudaFree(c->X); cudaFree(c->V); cudaFree(c->A); cudaFree(c->accum);
     cudaFree(c->packed[0]); cudaFree(c->packed[1]);
-    cudaFree(c->partial); cudaFree(c->counters); cudaFree(c->energy_part); cudaFree(c->stage);
+    cudaFree(c->partial); cudaFree(c->counters); cudaFree(c->energy_part); cudaFree(c->stage); cudaFree(c->frame);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -334,7 +337,7 @@ int nbody_create(nbody_ctx** out, const nbody_params* p)
     if (p->n_bodies <= 0) return fail(NBODY_E_INVALID, "n_bodies must be > 0 (got %d)", p->n_bodies);
     if (p->world < 1 || p->rank < 0 || p->rank >= p->world) return fail(NBODY_E_INVALID, "bad shard %d of %d", p->rank, p->world);
     const bool f64 = p->integrator == NBODY_INTEG_F64;
-    if (!f64 && p->integrator != NBODY_INTEG_F32) return fail(NBODY_E_INVALID, "unknown integrator %d", p->integrator);
+    if (!f64 && p->integrator != NBODY_INTEG_F32 && p->integrator != NBODY_INTEG_MIXED) return fail(NBODY_E_INVALID, "unknown integrator %d", p->integrator);
     // the self term is 0 * m / eps2^1.5 and the zero-mass padding sits at the
     // origin: both need eps2 > 0 to stay finite
     if (!((f64 ? p->eps2_f64 : (double)p->eps2) > 0.0)) return fail(NBODY_E_INVALID, "eps2 must be > 0");
@@ -423,3 +426,5 @@ int nbody_owned_range(nbody_ctx* c, int* begin, int* count)
 }  // extern "C"
 
 #include "nbody_engine_api.inl"
+#include "nbody_render.inl"
+#include "nbody_records.inl"

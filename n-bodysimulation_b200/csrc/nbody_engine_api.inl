@@ -15,6 +15,7 @@ int enqueue_full_step(nbody_ctx* c, cudaStream_t st)
     int rc = launch_force(c->var, c->plan_full, a, st);
     if (rc) return rc;
     c->cur ^= 1;
+    ++c->steps_done;
     return NBODY_OK;
 }
 
@@ -33,6 +34,7 @@ int nbody_upload(nbody_ctx* c, const float* x4, const float* v4)
     if (e == cudaSuccess) e = cudaMemsetAsync(c->packed[0], 0, (size_t)c->n_src_pad * sizeof(float4), c->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(c->packed[1], 0, (size_t)c->n_src_pad * sizeof(float4), c->stream);
     c->cur = 0;
+    c->steps_done = 0;
     for (int r = 0; r < c->p.world && e == cudaSuccess && rc == 0; ++r) {
         const int b = r * c->per;
         const int cnt = b >= c->n ? 0 : (c->n - b < c->per ? c->n - b : c->per);
@@ -170,6 +172,7 @@ int nbody_shard_remote_async(nbody_ctx* c, void* stream)
     rc = launch_force(c->var, c->plan_remote, a, st);
     if (rc) return rc;
     c->cur ^= 1;
+    ++c->steps_done;
     return NBODY_OK;
 }
 
@@ -188,7 +191,7 @@ struct Cached {
     int n_pad = 0;
 };
 std::mutex g_cache_mu;
-std::map<std::pair<int, int>, Cached> g_cache;   // (device, N)
+std::map<std::pair<std::pair<int, int>, int>, Cached> g_cache;   // ((device, N), variant)
 
 void free_cached(Cached& k)
 {
@@ -196,16 +199,17 @@ void free_cached(Cached& k)
     k = Cached();
 }
 
-int get_cached(int n, bool host_buffers, Cached** out)
+int get_cached(int n, bool host_buffers, Cached** out, int variant = NBODY_VARIANT_AUTO)
 {
     int dev = 0;
     CU(cudaGetDevice(&dev));
-    Cached& k = g_cache[std::make_pair(dev, n)];
+    Cached& k = g_cache[std::make_pair(std::make_pair(dev, n), variant)];
     if (!k.var) {
         cudaDeviceProp prop;
         CU(cudaGetDeviceProperties(&prop, dev));
         if (prop.major < 10) return fail(NBODY_E_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", dev, prop.major, prop.minor);
-        k.var = find_variant(auto_variant(n, n));
+        k.var = find_variant(variant == NBODY_VARIANT_AUTO ? auto_variant(n, n) : variant);
+        if (!k.var) { g_cache.erase(std::make_pair(std::make_pair(dev, n), variant)); return fail(NBODY_E_INVALID, "unknown kernel variant %d", variant); }
         k.n_pad = round_up(n, kSlotAlign);
         int rc = make_plan(k.var, prop.multiProcessorCount, 0, n, k.n_pad / k.var->UJ, &k.plan);
         if (rc) { k = Cached(); return rc; }
@@ -224,7 +228,7 @@ int get_cached(int n, bool host_buffers, Cached** out)
     return NBODY_OK;
 }
 
-int one_step_on_device(Cached* k, float4* dX, float4* dA, float4* dV, int n, float eps2, float dt, int f64, double dt64)
+int one_step_on_device(Cached* k, float4* dX, float4* dA, float4* dV, int n, float eps2, float dt, int f64, double dt64, int va_f3 = 0)
 {
     // snapshot of the step's start in packed form; X is then advanced in place
     int rc = launch_pack(dX, n, k->packed, 0, k->n_pad, 0);
@@ -235,7 +239,7 @@ int one_step_on_device(Cached* k, float4* dX, float4* dA, float4* dV, int n, flo
     a.src = k->packed;
     a.ra_begin = 0; a.ra_count = k->n_pad / k->var->UJ;
     a.partial = k->partial; a.counters = k->counters; a.maxseg = k->plan.maxseg;
-    a.eps2 = eps2; a.dt = dt; a.integ_f64 = f64; a.dt64 = dt64;
+    a.eps2 = eps2; a.dt = dt; a.integ_f64 = f64; a.dt64 = dt64; a.va_f3 = va_f3;
     return launch_force(k->var, k->plan, a, 0);
 }
 
@@ -283,13 +287,38 @@ int nbody_step_host_f3(float* h_bodies4, float* h_accel3, float* h_vel3, int n, 
     return NBODY_OK;
 }
 
+int nbody_step_opts_default(nbody_step_opts* o)
+{
+    if (!o) return fail(NBODY_E_INVALID, "null options");
+    o->eps2 = 0.002f; o->dt = 0.1f;   // TestProject/constants.h:25-26
+    o->integrator = NBODY_INTEG_F32; o->va_float3 = 0; o->variant = NBODY_VARIANT_AUTO;
+    return NBODY_OK;
+}
+
+int nbody_step_inplace_opts(float* d_bodies4, void* d_accel, void* d_vel, int n, const nbody_step_opts* o)
+{
+    if (!d_bodies4 || !d_accel || !d_vel || !o) return fail(NBODY_E_INVALID, "null pointer");
+    if (n <= 0) return fail(NBODY_E_INVALID, "N must be > 0 (got %d)", n);
+    if (!(o->eps2 > 0.f)) return fail(NBODY_E_INVALID, "eps2 must be > 0");
+    if (o->integrator != NBODY_INTEG_F32 && o->integrator != NBODY_INTEG_MIXED)
+        return fail(NBODY_E_INVALID, "integrator %d not valid for the in-place step", o->integrator);
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    Cached* k = nullptr;
+    int rc = get_cached(n, false, &k, o->variant);
+    if (rc) return rc;
+    rc = one_step_on_device(k, (float4*)d_bodies4, (float4*)d_accel, (float4*)d_vel, n, o->eps2, o->dt, o->integrator, 0.0, o->va_float3 ? 1 : 0);
+    if (rc) return rc;
+    CU(cudaDeviceSynchronize());
+    return NBODY_OK;
+}
+
 void nbody_release_cached(void)
 {
     std::lock_guard<std::mutex> lk(g_cache_mu);
     int cur = 0;
     cudaGetDevice(&cur);
     for (auto& kv : g_cache) {
-        cudaSetDevice(kv.first.first);
+        cudaSetDevice(kv.first.first.first);
         free_cached(kv.second);
     }
     g_cache.clear();

@@ -10,6 +10,9 @@
 //
 //   nbody_headless [--n N] [--steps S] [--ic reference|uniform|plummer] [--seed K]
 //                  [--eps2 E] [--dt D] [--resident] [--host-f3] [--json]
+//                  [--flavour simulate|emb|emb-float3]   which launcher of kernel.cuh:2-7 (headless forms)
+//                  [--ppm FILE]                          final frame (the reference's GL draw as CUDA)
+//                  [--save FILE] [--load FILE]           snapshot / resume (with --resident)
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -35,7 +38,9 @@ void fill_reference(float4* b, int n)
 }
 
 // main.cpp:142-160
-int simulationLoopNoVisual(float4* d_bodies, float4* d_accel, float4* d_vel, int n, int steps)
+// `after_first` (optional) is recorded after the first call: that call also loads the kernel
+// image and allocates the library's scratch, which the reference's launcher never had to do.
+int simulationLoopNoVisual(float4* d_bodies, float4* d_accel, float4* d_vel, int n, int steps, cudaEvent_t after_first = nullptr)
 {
     printf("Starting the simulation...\n");
     for (int counter = 0; counter < steps; ++counter) {
@@ -45,6 +50,7 @@ int simulationLoopNoVisual(float4* d_bodies, float4* d_accel, float4* d_vel, int
             std::cerr << e.what() << std::endl;
             return EXIT_FAILURE;
         }
+        if (counter == 0 && after_first) cudaEventRecord(after_first);
     }
     printf("Simulation complete\n");
     return 0;
@@ -64,7 +70,7 @@ int main(int argc, char** argv)
     int n = N_BODIES, steps = 10;
     unsigned long long seed = 12345;
     float eps2 = EPS2, dt = DT;
-    std::string ic = "reference";
+    std::string ic = "reference", flavour = "simulate", ppm, save, load;
     bool resident = false, host_f3 = false, json = false;
     for (int i = 1; i < argc; ++i) {
         auto need = [&](const char* f) { if (i + 1 >= argc) { fprintf(stderr, "%s needs a value\n", f); exit(2); } return argv[++i]; };
@@ -77,9 +83,15 @@ int main(int argc, char** argv)
         else if (!strcmp(argv[i], "--resident")) resident = true;
         else if (!strcmp(argv[i], "--host-f3")) host_f3 = true;
         else if (!strcmp(argv[i], "--json")) json = true;
+        else if (!strcmp(argv[i], "--flavour")) flavour = need("--flavour");
+        else if (!strcmp(argv[i], "--ppm")) ppm = need("--ppm");
+        else if (!strcmp(argv[i], "--save")) save = need("--save");
+        else if (!strcmp(argv[i], "--load")) load = need("--load");
         else { fprintf(stderr, "unknown flag %s\n", argv[i]); return 2; }
     }
     if (n <= 0 || steps < 0) { fprintf(stderr, "bad --n / --steps\n"); return 2; }
+    if ((!save.empty() || !load.empty()) && !resident) { fprintf(stderr, "--save / --load need --resident\n"); return 2; }
+    if (flavour != "simulate" && flavour != "emb" && flavour != "emb-float3") { fprintf(stderr, "unknown --flavour %s\n", flavour.c_str()); return 2; }
     const size_t size4 = sizeof(float4) * (size_t)n;
 
     float4 *bodies, *velocity, *accelerations;   // pinned, main.cpp:250-252
@@ -96,7 +108,7 @@ int main(int argc, char** argv)
     else { fprintf(stderr, "unknown --ic %s\n", ic.c_str()); return 2; }
 
     int rc = 0;
-    float ms = -1.f;
+    float ms = -1.f, ms_first = -1.f, ms_steady = -1.f;
     if (host_f3) {
         // headless-directory flavour: host pointers, float3 velocity (its constants: EPS2 0.002, DT 0.01)
         float3* v3 = new float3[n];
@@ -115,12 +127,16 @@ int main(int argc, char** argv)
         nbody_params_default(&p);
         p.n_bodies = n; p.eps2 = eps2; p.dt = dt;
         nbody_ctx* ctx = nullptr;
-        if (nbody_create(&ctx, &p) || nbody_upload(ctx, (float*)bodies, (float*)velocity)) { std::cerr << nbody_last_error() << std::endl; return EXIT_FAILURE; }
+        if (nbody_create(&ctx, &p) || (load.empty() ? nbody_upload(ctx, (float*)bodies, (float*)velocity) : nbody_snapshot_load(ctx, load.c_str()))) {
+            std::cerr << nbody_last_error() << std::endl;
+            return EXIT_FAILURE;
+        }
         printf("Starting the simulation...\n");
         if (nbody_step(ctx, steps)) { std::cerr << nbody_last_error() << std::endl; rc = EXIT_FAILURE; }
         else printf("Simulation complete\n");
         nbody_elapsed_ms(ctx, &ms);
         nbody_download(ctx, (float*)bodies, (float*)velocity, (float*)accelerations);
+        if (!save.empty() && nbody_snapshot_save(ctx, save.c_str())) { std::cerr << nbody_last_error() << std::endl; rc = EXIT_FAILURE; }
         nbody_destroy(ctx);
     } else {
         // the reference's own sequence: main.cpp:275-283,352-356
@@ -132,23 +148,57 @@ int main(int argc, char** argv)
         cudaMalloc((void**)&d_bodies, size4);
         cudaMemcpy(d_bodies, bodies, size4, cudaMemcpyHostToDevice);
         simulate_set_parameters(eps2, dt);
-        cudaEvent_t e0, e1;
-        cudaEventCreate(&e0); cudaEventCreate(&e1);
+        cudaEvent_t e0, e1, ef;
+        cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&ef);
         cudaEventRecord(e0);
-        rc = simulationLoopNoVisual(d_bodies, d_accelerations, d_velocity, n, steps);
+        if (flavour == "simulate") {
+            rc = simulationLoopNoVisual(d_bodies, d_accelerations, d_velocity, n, steps, ef);
+        } else {
+            // main.cpp:20-106 (simulationLoopVisualEmb / _float3) without the window: the float3 flavour
+            // views the same allocations as packed float3 arrays (they are large enough)
+            printf("Starting the simulation...\n");
+            try {
+                for (int s = 0; s < steps; ++s) {
+                    if (flavour == "emb") simulateHeadless_embParallel(d_bodies, d_accelerations, d_velocity, nullptr, n);
+                    else simulateHeadless_embParallel_float3(d_bodies, (float3*)d_accelerations, (float3*)d_velocity, nullptr, n);
+                    if (s == 0) cudaEventRecord(ef);
+                }
+                printf("Simulation complete\n");
+            } catch (const std::exception& e) { std::cerr << e.what() << std::endl; rc = EXIT_FAILURE; }
+        }
         cudaEventRecord(e1);
         cudaEventSynchronize(e1);
         cudaEventElapsedTime(&ms, e0, e1);
+        if (steps > 1 && rc == 0) { cudaEventElapsedTime(&ms_first, e0, ef); ms_steady = (ms - ms_first) / (steps - 1); }
         cudaMemcpy(bodies, d_bodies, size4, cudaMemcpyDeviceToHost);
         cudaMemcpy(velocity, d_velocity, size4, cudaMemcpyDeviceToHost);
         cudaMemcpy(accelerations, d_accelerations, size4, cudaMemcpyDeviceToHost);
         cudaFree(d_bodies); cudaFree(d_velocity); cudaFree(d_accelerations);
     }
+    if (!ppm.empty() && rc == 0) {
+        // what renderBodies + the shaders would have put in the window after the last step
+        nbody_view view;
+        nbody_view_default(&view);
+        const size_t fb = (size_t)view.width * view.height * 4;
+        float4* d_x = nullptr;
+        unsigned char* d_f = nullptr;
+        unsigned char* h_f = (unsigned char*)malloc(fb);
+        bool ok = cudaMalloc((void**)&d_x, size4) == cudaSuccess && cudaMalloc((void**)&d_f, fb) == cudaSuccess &&
+                  cudaMemcpy(d_x, bodies, size4, cudaMemcpyHostToDevice) == cudaSuccess &&
+                  nbody_render_device((const float*)d_x, n, &view, d_f) == NBODY_OK &&
+                  cudaMemcpy(h_f, d_f, fb, cudaMemcpyDeviceToHost) == cudaSuccess &&
+                  nbody_write_ppm(ppm.c_str(), h_f, view.width, view.height) == NBODY_OK;
+        if (!ok) { std::cerr << "frame: " << nbody_last_error() << std::endl; rc = EXIT_FAILURE; }
+        cudaFree(d_x); cudaFree(d_f); free(h_f);
+    }
     if (json && rc == 0) {
         const double inter = (double)n * (double)n * steps;
-        printf("{\"n\": %d, \"steps\": %d, \"ic\": \"%s\", \"device_ms\": %.4f, \"g_interactions_per_s\": %.3f, "
+        printf("{\"n\": %d, \"steps\": %d, \"ic\": \"%s\", \"flavour\": \"%s\", \"device_ms\": %.4f, \"g_interactions_per_s\": %.3f, "
+               "\"first_call_ms\": %.4f, \"steady_ms_per_step\": %.4f, \"steady_g_interactions_per_s\": %.3f, "
                "\"checksum_x\": %.9e, \"checksum_v\": %.9e, \"launches\": %lld}\n",
-               n, steps, ic.c_str(), ms, ms > 0 ? inter / (ms * 1e-3) / 1e9 : 0.0, checksum(bodies, n), checksum(velocity, n), nbody_launch_count());
+               n, steps, ic.c_str(), host_f3 ? "host-f3" : resident ? "resident" : flavour.c_str(), ms, ms > 0 ? inter / (ms * 1e-3) / 1e9 : 0.0,
+               ms_first, ms_steady, ms_steady > 0 ? (double)n * (double)n / (ms_steady * 1e-3) / 1e9 : 0.0,
+               checksum(bodies, n), checksum(velocity, n), nbody_launch_count());
     }
     nbody_release_cached();
     cudaFreeHost(bodies); cudaFreeHost(velocity); cudaFreeHost(accelerations);

@@ -46,7 +46,9 @@ struct ForceArgs {
     int maxseg;
     // parameters (TestProject/constants.h:25-26 at run time)
     float eps2, dt;
-    int integ_f64;        // 0: float integrator, 1: double (headless flavour)
+    int integ_f64;        // 0: float integrator (kernel.cu:116-124 / validation.cpp:43-49), 1: double (headless
+                          // flavour), 2: mixed (reduction flavours, kernel.cu:455-463: double half-kick, float drift)
+    int va_f3;            // 1: V and A are packed float3 arrays (FLOAT_3 build of the reference, main.cpp:233-269)
     double dt64;
     float k_one, k_negzero;   // 1.0f and -0.0f as run-time values (MODE 2 keeps ptxas from folding x*1+y)
 };
@@ -68,8 +70,14 @@ __device__ __forceinline__ void integrate_one(const ForceArgs& a, int gi, bool v
             return;
         }
         x = a.X[gi];
-        float4 v = a.V[gi];
-        if (!a.integ_f64) {
+        float4 v;
+        if (a.va_f3) {
+            const float* v3 = reinterpret_cast<const float*>(a.V) + 3 * (size_t)gi;
+            v = make_float4(v3[0], v3[1], v3[2], 0.f);
+        } else {
+            v = a.V[gi];
+        }
+        if (a.integ_f64 == 0) {
             const float hdt = 0.5f * a.dt;
             v.x = __fadd_rn(v.x, __fmul_rn(hdt, fx));
             v.y = __fadd_rn(v.y, __fmul_rn(hdt, fy));
@@ -77,7 +85,7 @@ __device__ __forceinline__ void integrate_one(const ForceArgs& a, int gi, bool v
             x.x = __fadd_rn(x.x, __fmul_rn(a.dt, v.x));
             x.y = __fadd_rn(x.y, __fmul_rn(a.dt, v.y));
             x.z = __fadd_rn(x.z, __fmul_rn(a.dt, v.z));
-        } else {
+        } else if (a.integ_f64 == 1) {
             // Sim-Without-OpenGL-Integration/kernel.cu:71-77: 0.5 * DT * a in double
             const double hdt = 0.5 * a.dt64;
             v.x = (float)((double)v.x + hdt * (double)fx);
@@ -86,10 +94,28 @@ __device__ __forceinline__ void integrate_one(const ForceArgs& a, int gi, bool v
             x.x = (float)((double)x.x + a.dt64 * (double)v.x);
             x.y = (float)((double)x.y + a.dt64 * (double)v.y);
             x.z = (float)((double)x.z + a.dt64 * (double)v.z);
+        } else {
+            // TestProject/kernel.cu:455-463 (inter_block_reduction*): `0.5 * DT * a` promotes the
+            // half-kick to double (DT is a float literal there); the drift `DT * v` stays float and is
+            // an FMA in the reference's GPU build (nvcc -fmad default).
+            const double hdt = 0.5 * (double)a.dt;
+            v.x = (float)((double)v.x + hdt * (double)fx);
+            v.y = (float)((double)v.y + hdt * (double)fy);
+            v.z = (float)((double)v.z + hdt * (double)fz);
+            x.x = fmaf(a.dt, v.x, x.x);
+            x.y = fmaf(a.dt, v.y, x.y);
+            x.z = fmaf(a.dt, v.z, x.z);
         }
         a.X[gi] = x;
-        a.V[gi] = v;
-        a.A[gi] = make_float4(fx, fy, fz, 0.f);
+        if (a.va_f3) {
+            float* v3 = reinterpret_cast<float*>(a.V) + 3 * (size_t)gi;
+            float* a3 = reinterpret_cast<float*>(a.A) + 3 * (size_t)gi;
+            v3[0] = v.x; v3[1] = v.y; v3[2] = v.z;
+            a3[0] = fx; a3[1] = fy; a3[2] = fz;
+        } else {
+            a.V[gi] = v;
+            a.A[gi] = make_float4(fx, fy, fz, 0.f);
+        }
     } else if (a.accum_out) {
         return;
     }

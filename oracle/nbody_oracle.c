@@ -228,3 +228,86 @@ int oracle_num_threads(void)
     return 1;
 #endif
 }
+
+/* Reduction-flavour step (TestProject/kernel.cu:163-246 kernel_reduction +
+ * :406-436 inter_block_reduction; float3 twin :250-318 + :439-469), snapshot
+ * semantics.  Pair math as validation.cpp:9-24; the integrator is the one of
+ * inter_block_reduction: `v += 0.5 * DT * a` evaluates in DOUBLE (0.5 is a
+ * double literal, DT a float macro) and rounds once; `x += DT * v` is float
+ * and -- that code exists only as GPU code, built by nvcc with its default
+ * -fmad=true -- one fused multiply-add.  PARITY UNPINNED for this flavour:
+ * the reference has no CPU twin of it and it cannot run here (it needs an
+ * OpenGL-mapped buffer); only the pair sum is pinned (shared with O2).
+ * V, A: float[stride*N], stride 4 (float4, A.w = 0) or 3 (float3). */
+void oracle_step_mixed(float *X, float *A, float *V, int N, float eps2, float dt, int stride)
+{
+    float *S = (float *)malloc((size_t)N * 4 * sizeof(float));
+    memcpy(S, X, (size_t)N * 4 * sizeof(float));
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < N; ++i) {
+        float a[3] = { 0.0f, 0.0f, 0.0f };
+        for (int j = 0; j < N; ++j)
+            if (i != j) pair_f32(S + 4*i, S + 4*j, a, eps2);
+        for (int c = 0; c < 3; ++c) {
+            float v = (float)((double)V[stride*i+c] + 0.5 * (double)dt * (double)a[c]);
+            V[stride*i+c] = v;
+            X[4*i+c] = fmaf(dt, v, X[4*i+c]);
+            A[stride*i+c] = a[c];
+        }
+        if (stride == 4) A[4*i+3] = 0.0f;
+    }
+    free(S);
+}
+
+/* ---- point-splat frame --------------------------------------------------
+ * CPU restatement of what the reference draws each step:
+ * TestProject/simulation_visualization.cpp:15-37 (vertex shader: weight and
+ * NDC position), :40-56 (fragment shader: mix(green, red, weight), alpha 1),
+ * :132-135 (depth test on, 1-pixel points), :165-169 (glDrawArrays GL_POINTS
+ * in body order), main.cpp:48 (clear colour and depth every frame), uniforms
+ * :203-207, window 800x600 (simulation_visualization.h:8-9).
+ * Fixed-function steps are restated per the OpenGL 3.3 spec: a point whose
+ * clip-space position lies outside [-1,1]^3 is clipped; window coordinates
+ * xw = (ndc.x+1)*W/2, yw = (ndc.y+1)*H/2, the 1-pixel point covers pixel
+ * (floor(xw), floor(yw)); depth = (ndc.z+1)/2 compared with GL_LESS against a
+ * buffer cleared to 1 (kept here as float); colour written as
+ * round(c*255).  Rows are stored top-down (image order), GL's y up.
+ * depth_test = 0 restates the frame with the test off (last body drawn wins),
+ * which is what a driver does if glEnable ran before a context existed
+ * (setupOpenGL() is called before glfwInit(), :183-184).
+ * PARITY UNPINNED: no GL stack exists on this box to produce a reference frame.
+ * rgba: uint8[4*W*H], cleared to (0,0,0,0). */
+void oracle_render(const float *X, int N, int W, int H, float max_x, float max_y, float max_z,
+                   float min_w, float max_w, int depth_test, unsigned char *rgba)
+{
+    float *zbuf = (float *)malloc((size_t)W * H * sizeof(float));
+    for (int p = 0; p < W * H; ++p) zbuf[p] = 1.0f;
+    memset(rgba, 0, (size_t)W * H * 4);
+    const float mx[3] = { max_x, max_y, max_z };
+    for (int i = 0; i < N; ++i) {
+        float ndc[3];
+        int inside = 1;
+        for (int c = 0; c < 3; ++c) {
+            ndc[c] = 2.0f * (X[4*i+c] - (-mx[c])) / (mx[c] - (-mx[c])) - 1.0f;
+            if (!(ndc[c] >= -1.0f && ndc[c] <= 1.0f)) inside = 0;
+        }
+        if (!inside) continue;
+        const float xw = (ndc[0] + 1.0f) * ((float)W * 0.5f), yw = (ndc[1] + 1.0f) * ((float)H * 0.5f);
+        const int px = (int)floorf(xw), py = (int)floorf(yw);
+        if (px < 0 || px >= W || py < 0 || py >= H) continue;   /* ndc == +1 exactly */
+        const float depth = (ndc[2] + 1.0f) * 0.5f;
+        const int p = (H - 1 - py) * W + px;
+        if (depth_test && !(depth < zbuf[p])) continue;
+        zbuf[p] = depth;
+        float wgt = (X[4*i+3] - min_w) / (max_w - min_w);
+        /* mix(a, b, t) = a*(1-t) + b*t per the GLSL spec; written to an 8-bit UNORM target */
+        float r = 0.0f * (1.0f - wgt) + 1.0f * wgt, g = 1.0f * (1.0f - wgt) + 0.0f * wgt;
+        r = r < 0.0f ? 0.0f : (r > 1.0f ? 1.0f : r);
+        g = g < 0.0f ? 0.0f : (g > 1.0f ? 1.0f : g);
+        rgba[4*p+0] = (unsigned char)(int)floorf(r * 255.0f + 0.5f);
+        rgba[4*p+1] = (unsigned char)(int)floorf(g * 255.0f + 0.5f);
+        rgba[4*p+2] = 0;
+        rgba[4*p+3] = 255;
+    }
+    free(zbuf);
+}

@@ -136,3 +136,20 @@ def norm_rel_err(a, b):
     den = np.linalg.norm(b, axis=1)
     den = np.where(den > 0, den, 1.0)
     return float(np.max(np.linalg.norm(a - b, axis=1) / den))
+
+
+def step_mixed(X, A, V, eps2=0.002, dt=0.1):
+    """reduction flavours (kernel.cu:406-436 / :439-469): double half-kick, float FMA drift.
+    V, A are (N,4) or (N,3) float32.  Parity unpinned (GPU-only reference code)."""
+    stride = V.shape[1]
+    assert A.shape[1] == stride and stride in (3, 4)
+    _lib.oracle_step_mixed(_fp(X), _fp(A), _fp(V), len(X), C.c_float(eps2), C.c_float(dt), C.c_int(stride))
+
+
+def render(X, width=800, height=600, max_xyz=(2e5, 2e5, 2e5), min_w=1e5, max_w=1e9, depth_test=True):
+    """point-splat frame of simulation_visualization.cpp's shaders; returns uint8 (H, W, 4), top row first"""
+    img = np.zeros((height, width, 4), np.uint8)
+    _lib.oracle_render(_fp(X), len(X), C.c_int(width), C.c_int(height), C.c_float(max_xyz[0]), C.c_float(max_xyz[1]),
+                       C.c_float(max_xyz[2]), C.c_float(min_w), C.c_float(max_w), C.c_int(1 if depth_test else 0),
+                       img.ctypes.data_as(C.c_void_p))
+    return img
