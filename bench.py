@@ -41,6 +41,8 @@ def parse():
     ap.add_argument("--bodies", "--n", dest="n", type=int, default=1 << 20)   # torchrun swallows a bare --n: use --bodies there
     ap.add_argument("--ic", default="uniform", choices=["uniform", "plummer"])
     ap.add_argument("--variant", type=int, default=0)
+    ap.add_argument("--exchange", default="nccl", choices=["nccl", "p2p"],
+                    help="multi-GPU position exchange: NCCL all-gather overlapped with the own-slice kernel, or P2P stores fused into the epilogue")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -49,7 +51,25 @@ def parse():
 def config_of(args, world):
     return {"workload": f"N={args.n} bodies, {args.ic} ICs, EPS2=0.002 DT=0.1 (constants.h), one all-pairs step + integrator per step",
             "n_bodies": args.n, "ic": args.ic, "sharding": f"targets/{world}" if world > 1 else "none",
+            "exchange": (args.exchange if world > 1 else "none"),
             "l2": "flushed between timed steps (256 MiB memset, untimed)"}
+
+
+def ncu_traffic(n, kernel):
+    """DRAM bytes per launch of the force kernel from the committed `ncu --set full` capture
+    (profiles/r1_ncu_full_v45_n1m_raw.csv: dram__bytes_read.sum + dram__bytes_write.sum); None when
+    no capture exists for this (N, kernel)."""
+    if n != (1 << 20) or not kernel.startswith("T6_NT256_UJ256_U2_1_B1"):
+        return None
+    try:
+        tot = 0.0
+        for line in open(os.path.join(ROOT, "profiles", "r1_ncu_full_v45_n1m_raw.csv")):
+            f = line.strip().split(",")
+            if f[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                tot += float(f[2]) * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[f[1]]
+        return int(tot) if tot > 0 else None
+    except Exception:  # noqa: BLE001
+        return None
 
 
 def peaks():
@@ -174,7 +194,7 @@ def run_ours(args):
         eps2, dt = 0.002, 0.1
     sim = nb.Simulation(n, eps2=eps2, dt=dt, rank=rank, world=world, device=local, variant=args.variant)
     sim.upload(x0, v0)
-    runner = par.ShardedSimulation(sim, rank, world, device=dev)
+    runner = par.ShardedSimulation(sim, rank, world, device=dev, exchange=args.exchange)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
     def barrier():
@@ -190,7 +210,7 @@ def run_ours(args):
             e0.record()
         runner.step()
         with torch.cuda.stream(runner.comm):
-            if world == 1:
+            if world == 1 or runner.exchange == "p2p":   # nothing runs on the comm stream then
                 runner.comm.wait_stream(runner.compute)
             e1.record()
         runner.synchronize()
@@ -254,7 +274,8 @@ def run_ours(args):
     peak_tflops = sms * 128 * 2 * pk["sm_max_mhz"] * 1e6 / 1e12
     achieved = FLOP_PER_INTERACTION * value * 1e9 / 1e12 / world          # per GPU, TFLOP/s
     roof = {"bound": "fp32", "achieved": round(achieved, 3), "peak": round(peak_tflops, 3), "unit": "TFLOP/s",
-            "frac": round(achieved / peak_tflops, 4), "traffic": None,
+            "frac": round(achieved / peak_tflops, 4), "traffic": ncu_traffic(n, info["variant_name"]) if world == 1 else None,
+            "traffic_unit": "DRAM bytes per launch (ncu --set full, profiles/r1_ncu_full_v45_n1m_raw.csv); algorithmic 112*N = 117 MB",
             "peak_src": f"nominal FP32: {sms} SMs x 128 lanes x 2 x {pk['sm_max_mhz']:.0f} MHz ({pk['src']}); "
                         "MEASURED_PEAKS.json holds HBM and bf16-tensor peaks only, neither bounds this kernel",
             "kernel": info["variant_name"], "launches_per_step": launches / K}

@@ -113,6 +113,20 @@ int nbody_shard_remote_async(nbody_ctx* ctx, void* stream);
  * (read by the next local/remote calls), 1 = next.  slot_bytes is the size of
  * one rank's slice (all slices equal; own slice starts at rank*slot_bytes). */
 int nbody_shard_sources(nbody_ctx* ctx, int which, void** dptr, size_t* total_bytes, size_t* slot_bytes);
+/* Fused exchange.  Instead of all-gathering the new positions after the step, the
+ * step's epilogue stores each new position into its slot of EVERY rank's next
+ * source buffer (16-byte P2P stores over NVLink / NVSwitch): one kernel per step
+ * over all sources, no gather, no partial-sum round trip.  The caller needs one
+ * cross-rank barrier between steps (any tiny collective on the same stream).
+ *   - other processes: exchange nbody_shard_ipc_handles() (2 x 64 bytes, the CUDA IPC
+ *     handles of the two source buffers) and attach each peer with nbody_shard_attach_ipc;
+ *   - same process (several contexts, e.g. tests): nbody_shard_buffers + nbody_shard_attach_ptr.
+ * All ranks must step in lock step from the same upload (buffer parity is shared). */
+int nbody_shard_ipc_handles(nbody_ctx* ctx, void* handles128);
+int nbody_shard_attach_ipc(nbody_ctx* ctx, int peer_rank, const void* handles128);
+int nbody_shard_buffers(nbody_ctx* ctx, void** buf0, void** buf1);
+int nbody_shard_attach_ptr(nbody_ctx* ctx, int peer_rank, void* buf0, void* buf1);
+int nbody_shard_step_fused_async(nbody_ctx* ctx, void* stream);
 /* Geometry helper: bytes of one rank's padded slice for (N, world). */
 size_t nbody_shard_slot_bytes(int n_bodies, int world);
 

@@ -68,6 +68,11 @@ SIGNATURES = {
     "nbody_shard_remote_async": (C.c_int, [_vp, _vp]),
     "nbody_shard_sources": (C.c_int, [_vp, C.c_int, C.POINTER(_vp), C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
     "nbody_shard_slot_bytes": (C.c_size_t, [C.c_int, C.c_int]),
+    "nbody_shard_ipc_handles": (C.c_int, [_vp, _vp]),
+    "nbody_shard_attach_ipc": (C.c_int, [_vp, C.c_int, _vp]),
+    "nbody_shard_buffers": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp)]),
+    "nbody_shard_attach_ptr": (C.c_int, [_vp, C.c_int, _vp, _vp]),
+    "nbody_shard_step_fused_async": (C.c_int, [_vp, _vp]),
     "nbody_step_inplace_f4": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_float, C.c_float]),
     "nbody_step_host_f3": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_double, C.c_double]),
     "nbody_step_opts_default": (C.c_int, [C.POINTER(NBodyStepOpts)]),
@@ -308,6 +313,27 @@ class Simulation:
 
     def shard_remote_async(self, stream: int = 0) -> None:
         _check(lib.nbody_shard_remote_async(self._h, stream))
+
+    # fused exchange: the epilogue stores new positions into every peer's next buffer (P2P)
+    def shard_ipc_handles(self) -> bytes:
+        buf = C.create_string_buffer(128)
+        _check(lib.nbody_shard_ipc_handles(self._h, buf))
+        return buf.raw
+
+    def shard_attach_ipc(self, peer: int, handles: bytes) -> None:
+        assert len(handles) == 128
+        _check(lib.nbody_shard_attach_ipc(self._h, peer, C.create_string_buffer(handles, 128)))
+
+    def shard_buffers(self):
+        a, b = _vp(), _vp()
+        _check(lib.nbody_shard_buffers(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def shard_attach_ptr(self, peer: int, buf0: int, buf1: int) -> None:
+        _check(lib.nbody_shard_attach_ptr(self._h, peer, buf0, buf1))
+
+    def shard_step_fused_async(self, stream: int = 0) -> None:
+        _check(lib.nbody_shard_step_fused_async(self._h, stream))
 
     def shard_sources(self, which: int = 0):
         p, tot, slot = _vp(), C.c_size_t(), C.c_size_t()

@@ -176,6 +176,86 @@ int nbody_shard_remote_async(nbody_ctx* c, void* stream)
     return NBODY_OK;
 }
 
+// ---- fused exchange: epilogue stores into the peers' next buffers -----------------------------------
+int nbody_shard_ipc_handles(nbody_ctx* c, void* handles128)
+{
+    if (!c || !handles128) return fail(NBODY_E_INVALID, "null argument");
+    int rc = set_device(c);
+    if (rc) return rc;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handles are 64 bytes");
+    cudaIpcMemHandle_t h[2];
+    CU(cudaIpcGetMemHandle(&h[0], c->packed[0]));
+    CU(cudaIpcGetMemHandle(&h[1], c->packed[1]));
+    memcpy(handles128, h, sizeof h);
+    return NBODY_OK;
+}
+
+static int attach_checks(nbody_ctx* c, int peer)
+{
+    if (!c) return fail(NBODY_E_INVALID, "null context");
+    if (c->p.world < 2) return fail(NBODY_E_STATE, "an unsharded context has no peers");
+    if (c->p.world > kMaxPeers + 1) return fail(NBODY_E_STATE, "fused exchange supports up to %d ranks", kMaxPeers + 1);
+    if (peer < 0 || peer >= c->p.world || peer == c->p.rank) return fail(NBODY_E_INVALID, "bad peer rank %d (this is rank %d of %d)", peer, c->p.rank, c->p.world);
+    if (c->peer_packed[peer][0]) return fail(NBODY_E_STATE, "peer %d is already attached", peer);
+    return set_device(c);
+}
+
+int nbody_shard_attach_ipc(nbody_ctx* c, int peer, const void* handles128)
+{
+    int rc = attach_checks(c, peer);
+    if (rc) return rc;
+    if (!handles128) return fail(NBODY_E_INVALID, "null handles");
+    cudaIpcMemHandle_t h[2];
+    memcpy(h, handles128, sizeof h);
+    void *p0 = nullptr, *p1 = nullptr;
+    CU(cudaIpcOpenMemHandle(&p0, h[0], cudaIpcMemLazyEnablePeerAccess));
+    cudaError_t e = cudaIpcOpenMemHandle(&p1, h[1], cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) { cudaIpcCloseMemHandle(p0); return fail(NBODY_E_CUDA, "cudaIpcOpenMemHandle: %s", cudaGetErrorString(e)); }
+    c->peer_packed[peer][0] = (float4*)p0; c->peer_packed[peer][1] = (float4*)p1;
+    c->peer_ipc[peer] = true;
+    ++c->peers_attached;
+    return NBODY_OK;
+}
+
+int nbody_shard_attach_ptr(nbody_ctx* c, int peer, void* buf0, void* buf1)
+{
+    int rc = attach_checks(c, peer);
+    if (rc) return rc;
+    if (!buf0 || !buf1) return fail(NBODY_E_INVALID, "null buffer");
+    c->peer_packed[peer][0] = (float4*)buf0; c->peer_packed[peer][1] = (float4*)buf1;
+    ++c->peers_attached;
+    return NBODY_OK;
+}
+
+int nbody_shard_buffers(nbody_ctx* c, void** buf0, void** buf1)
+{
+    if (!c || !buf0 || !buf1) return fail(NBODY_E_INVALID, "null argument");
+    *buf0 = c->packed[0]; *buf1 = c->packed[1];
+    return NBODY_OK;
+}
+
+int nbody_shard_step_fused_async(nbody_ctx* c, void* stream)
+{
+    if (!c) return fail(NBODY_E_INVALID, "null context");
+    int rc = set_device(c);
+    if (rc) return rc;
+    cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
+    if (c->p.world == 1) return enqueue_full_step(c, st);
+    if (c->peers_attached != c->p.world - 1) return fail(NBODY_E_STATE, "%d of %d peers attached", c->peers_attached, c->p.world - 1);
+    ForceArgs a = base_args(c);
+    a.ra_begin = 0; a.ra_count = c->n_src_pad / c->var->UJ;
+    a.next_src = c->packed[c->cur ^ 1];
+    a.next_off = c->p.rank * c->slot_bodies;
+    a.maxseg = c->plan_full.maxseg;
+    for (int r = 0; r < c->p.world; ++r)
+        if (r != c->p.rank) a.peer_next[a.n_peer++] = c->peer_packed[r][c->cur ^ 1];
+    rc = launch_force(c->var, c->plan_full, a, st);
+    if (rc) return rc;
+    c->cur ^= 1;
+    ++c->steps_done;
+    return NBODY_OK;
+}
+
 }  // extern "C"
 
 // ---- reference-shaped one-call entry points ------------------------------------------------------------

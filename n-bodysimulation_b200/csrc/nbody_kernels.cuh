@@ -23,6 +23,7 @@ namespace nbody {
 
 constexpr int kStages = 4;           // shared-memory ring depth
 constexpr int kLookahead = kStages - 2;  // tiles in flight ahead of the consumers
+constexpr int kMaxPeers = 15;        // other GPUs a context can store to (one NVSwitch domain)
 
 struct ForceArgs {
     // owned targets, AoS float4, indexed 0..n_targets (caller-visible layout)
@@ -37,6 +38,10 @@ struct ForceArgs {
     // new positions of the owned targets in packed layout (may be null)
     float4* next_src;
     int next_off;         // packed body index of target 0 (even)
+    // fused exchange (multi-GPU): the same 16-byte stores also go to every peer's NEXT buffer
+    // (peer memory mapped over NVLink), replacing the all-gather of the new positions
+    float4* peer_next[kMaxPeers];
+    int n_peer;
     // two-phase accumulation (sharded runs)
     const float4* accum_in;   // added first when non-null
     float4* accum_out;        // when non-null: store sums here, do not integrate
@@ -128,7 +133,11 @@ __device__ __forceinline__ void integrate_one(const ForceArgs& a, int gi, bool v
         const float r1 = __shfl_xor_sync(0xffffffffu, s1, 1);
         const float4 o = odd ? make_float4(r0, x.z, r1, x.w) : make_float4(x.x, r0, x.y, r1);
         const bool pair_valid = __shfl_xor_sync(0xffffffffu, (int)valid, 1) || valid;
-        if (pair_valid) a.next_src[(size_t)(a.next_off + gi - (int)odd) + (odd ? 1 : 0)] = o;
+        if (pair_valid) {
+            const size_t at = (size_t)(a.next_off + gi - (int)odd) + (odd ? 1 : 0);
+            a.next_src[at] = o;
+            for (int p = 0; p < a.n_peer; ++p) a.peer_next[p][at] = o;   // P2P stores (NVLink)
+        }
     }
 }
 

@@ -9,6 +9,13 @@ interactions against the rank's own slice:
     compute stream :  local(own x own) ------------------> remote(own x others)+integrate
     comm stream    :  all_gather(new positions, in place) -^   (event)
 
+`exchange="p2p"` replaces the gather by a FUSED exchange: every rank maps its peers' source
+buffers (CUDA IPC handles passed around with all_gather_object) and the step kernel's epilogue
+stores each new position straight into every rank's next buffer over NVLink -- one kernel per
+step over all sources, then a 4-byte all-reduce on the same stream as the cross-rank barrier:
+
+    compute stream :  fused step (own targets x all sources; epilogue -> own + peers' next buffers) | barrier
+
 Body order and slot geometry come from the C ABI (nbody_shard_sources): rank r's
 slice sits at byte offset r*slot_bytes of the packed source buffer, so the
 in-place all-gather (`input` = own slice view of `output`) needs no staging copy.
@@ -36,7 +43,7 @@ class ShardedSimulation:
     object with shard_local_async / shard_remote_async / shard_sources (the gloo CPU test
     passes a host-memory stand-in).  `group` is a torch.distributed process group."""
 
-    def __init__(self, sim, rank: int, world: int, group=None, device=None, overlap: bool = True):
+    def __init__(self, sim, rank: int, world: int, group=None, device=None, overlap: bool = True, exchange: str = "nccl"):
         import torch
         import torch.distributed as dist
         self.torch, self.dist = torch, dist
@@ -48,6 +55,17 @@ class ShardedSimulation:
             self.compute = torch.cuda.Stream(device=device)
             self.comm = torch.cuda.Stream(device=device)
         self.steps_done = 0
+        assert exchange in ("nccl", "p2p")
+        self.exchange = exchange if world > 1 else "nccl"
+        if self.exchange == "p2p":
+            # every rank opens every other rank's two source buffers (cudaIpcOpenMemHandle)
+            mine = sim.shard_ipc_handles()
+            handles = [None] * world
+            dist.all_gather_object(handles, mine, group=group)
+            for r in range(world):
+                if r != rank:
+                    sim.shard_attach_ipc(r, handles[r])
+            self._flag = torch.zeros(1, dtype=torch.int32, device=device if device is not None else "cpu")
 
     def _source_views(self, which: int):
         ptr, total, slot = self.sim.shard_sources(which)
@@ -70,6 +88,20 @@ class ShardedSimulation:
         (work may still be in flight on self.compute / self.comm when overlapping)"""
         if self.world == 1:
             self.sim.shard_local_async(self.compute.cuda_stream if self.overlap else 0)
+            self.steps_done += 1
+            return
+        if self.exchange == "p2p":
+            torch = self.torch
+            # barrier after the step: my stores have left (kernel complete) and every peer's have landed
+            # before the next step reads them; also nobody overwrites a buffer a peer is still reading
+            if self.device is None or torch.device(self.device).type != "cuda":
+                self.sim.shard_step_fused_async(0)
+                self.dist.all_reduce(self._flag, group=self.group)
+            else:
+                st = self.compute if self.overlap else torch.cuda.current_stream(self.device)
+                self.sim.shard_step_fused_async(st.cuda_stream)
+                with torch.cuda.stream(st):
+                    self.dist.all_reduce(self._flag, group=self.group)
             self.steps_done += 1
             return
         if not self.overlap:
