@@ -51,8 +51,9 @@ struct Variant {
     int T, NT, UJ, unroll, packed, minb;
     int cs, cmode;   // cluster size (1 = none); 1 = TMA multicast of source units, 2 = j-split + DSMEM reduction
     void (*kernel)(const ForceArgs);
-    size_t smem() const { return (size_t)kStages * UJ * 16 + 16 * kStages + 16 + (cmode == 2 ? (size_t)TI() * 16 : 0); }
-    int TI() const { return T * NT; }
+    int small = 0;   // 1: small_kernel (T = targets per CTA, sources split over the CTA's threads, shuffle reduction)
+    size_t smem() const { return small ? 0 : (size_t)kStages * UJ * 16 + 16 * kStages + 16 + (cmode == 2 ? (size_t)TI() * 16 : 0); }
+    int TI() const { return small ? T : T * NT; }
     int TS() const { return cmode == 1 ? TI() * cs : TI(); }          // targets per worker tile
 };
 
@@ -61,6 +62,8 @@ struct Variant {
 #define CVARIANT(id, T, NT, UJ, UN, PK, MB, CS, CM) \
     { id, "T" #T "_NT" #NT "_UJ" #UJ "_U" #UN "_" #PK "_B" #MB "_C" #CS "m" #CM, T, NT, UJ, UN, PK, MB, CS, CM, force_kernel<T, NT, UJ, UN, PK, MB, CS, CM> }
 
+#define SVARIANT(id, TT, NT, UN) \
+    { id, "S_TT" #TT "_NT" #NT "_U" #UN, TT, NT, 64, UN, 1, 1, 1, 0, small_kernel<TT, NT, UN>, 1 }
 // packed = FFMA2 path, 0 = scalar FFMA path (kept for the with/without evidence)
 const Variant kVariants[] = {
     VARIANT(1, 4, 256, 256, 4, 1, 2),
@@ -127,6 +130,14 @@ const Variant kVariants[] = {
     CVARIANT(68, 1, 128, 64, 8, 1, 8, 4, 2),
     CVARIANT(69, 2, 128, 128, 8, 1, 6, 8, 2),
     CVARIANT(70, 6, 256, 256, 2, 1, 1, 8, 2),
+    // small-N family: j-split inside the CTA, warp-shuffle reduction, no scratch
+    SVARIANT(80, 8, 128, 2),
+    SVARIANT(81, 8, 256, 2),
+    SVARIANT(82, 4, 128, 2),
+    SVARIANT(83, 16, 256, 1),
+    SVARIANT(84, 8, 64, 2),
+    SVARIANT(85, 2, 128, 4),
+    SVARIANT(86, 8, 512, 1),
 };
 const int kNumVariants = (int)(sizeof kVariants / sizeof kVariants[0]);
 constexpr int kSlotAlign = 1024;   // bodies; multiple of every variant's UJ
@@ -140,9 +151,12 @@ const Variant* find_variant(int id)
 
 int auto_variant(int n_targets, int n_sources)
 {
-    (void)n_sources;
     // best of the r1 sweeps (profiles/r1_variant_sweep_*.jsonl); the cluster variants (60-70)
     // measured neutral (C2 multicast) or slower (C4/C8, DSMEM j-split) and are opt-in only
+    if (n_sources < 12288) {             // a step is < 50 us: latency decides -> small-N family
+        if (n_sources < 3072) return 85; // 2 targets / CTA, sources split over 128 threads, shuffle reduction
+        return 82;                       // 4 targets / CTA
+    }
     if (n_targets >= 12288) return 45;   // T6 x 256 threads, 1 CTA/SM
     if (n_targets >= 2048) return 3;     // T2 x 256 threads, 3 CTAs/SM
     return 12;                           // T1 x 128 threads, 64-body units
@@ -159,6 +173,15 @@ struct Plan {
 int make_plan(const Variant* v, int sm_count, int grid_override, int n_targets, int J, Plan* out)
 {
     Plan pl;
+    if (v->small) {   // one CTA per T targets, every CTA visits all J units: nothing to cut, no scratch
+        (void)sm_count; (void)grid_override; (void)J;
+        pl.occ = 1;
+        pl.num_itiles = (n_targets + v->T - 1) / v->T;
+        pl.grid = pl.num_itiles;
+        pl.maxseg = 1; pl.num_counters = 1; pl.partial_bytes = sizeof(float4);
+        *out = pl;
+        return NBODY_OK;
+    }
     CU(cudaFuncSetAttribute(v->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v->smem()));
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pl.occ, v->kernel, v->NT, v->smem()));
     if (pl.occ < 1) return fail(NBODY_E_CUDA, "variant %s does not fit on an SM", v->name);
@@ -302,6 +325,7 @@ int nbody_variant_info(int id, char* buf, size_t buflen)
     if (v && buf && buflen) {
         char cl[96] = "";
         if (v->cs > 1) snprintf(cl, sizeof cl, ", clusters of %d CTAs (%s)", v->cs, v->cmode == 1 ? "TMA multicast of source units" : "j-split, DSMEM reduction");
+        if (v->small) snprintf(cl, sizeof cl, ", small-N family: %d targets/CTA, sources split over the CTA, warp-shuffle reduction", v->T);
         snprintf(buf, buflen, "%s: %d targets/thread, %d threads/CTA, %d sources/tile, unroll %d pairs, %s FP32, min %d CTAs/SM, %zu B smem%s",
                  v->name, v->T, v->NT, v->UJ, v->unroll,
                  v->packed == 0 ? "scalar" : v->packed == 1 ? "packed f32x2" : v->packed == 2 ? "packed f32x2 (all FFMA2)" : v->packed == 3 ? "packed f32x2 + prefetch" : "packed f32x2 + first-pair prefetch",

@@ -476,6 +476,98 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
     if (CS > 1) cluster_sync_all();   // no CTA leaves while peers may still touch its shared memory
 }
 
+// ---- small-N kernel: j-split inside the CTA, warp-shuffle reduction ---------------------------------
+// Below a few thousand bodies a step is a handful of microseconds and the stream-K machinery
+// (TMA ring, partial sums through global memory, last-arriver fix-up) is mostly latency.  Here a
+// CTA owns TT targets, every thread keeps ALL of them in registers and takes every NT-th source
+// pair straight from the packed buffer (two coalesced LDG.128 per pair, L2-resident: the whole
+// system is <= 128 KB), so the source range is split across the threads of the CTA; the NT
+// partial sums per target are combined by shfl.xor inside each warp and through shared memory
+// across the warps, in fixed order (deterministic), and warp 0 runs the same fused integrator.
+// One launch, no scratch, no atomics.  Same ForceArgs as force_kernel (both source ranges, the
+// two-phase accumulators and the peer stores of the fused exchange work unchanged); UJ = 64.
+template <int TT, int NT, int UNROLL>
+__global__ void __launch_bounds__(NT) small_kernel(const ForceArgs a)
+{
+    constexpr int UJ = 64, NW = NT / 32;
+    static_assert(TT % 2 == 0 && TT <= 32 && NT % 32 == 0, "targets per CTA: even, at most one warp");
+    __shared__ float s_part[NW][3 * TT];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int g0 = blockIdx.x * TT;
+
+    u64 nx[TT], ny[TT], nz[TT], ax[TT], ay[TT], az[TT];
+#pragma unroll
+    for (int t = 0; t < TT; ++t) {
+        float4 xi = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (g0 + t < a.n_targets) xi = __ldg(a.X + g0 + t);
+        nx[t] = pack2(-xi.x, -xi.x); ny[t] = pack2(-xi.y, -xi.y); nz[t] = pack2(-xi.z, -xi.z);
+        ax[t] = 0ull; ay[t] = 0ull; az[t] = 0ull;
+    }
+    const u64 eps2p = pack2(a.eps2, a.eps2);
+    const int pairs_a = a.ra_count * (UJ / 2), pairs = pairs_a + a.rb_count * (UJ / 2);
+    const ulonglong2* src = reinterpret_cast<const ulonglong2*>(a.src);
+    auto pair_at = [&](int p) -> size_t {   // packed index (in float4 units / 2) of pair p of range A|B
+        return p < pairs_a ? (size_t)a.ra_begin * (UJ / 2) + p : (size_t)a.rb_begin * (UJ / 2) + (p - pairs_a);
+    };
+#pragma unroll 1
+    for (int p0 = tid; p0 < pairs; p0 += NT * UNROLL) {
+        ulonglong2 xy[UNROLL], zm[UNROLL];
+#pragma unroll
+        for (int q = 0; q < UNROLL; ++q) {
+            const int p = p0 + q * NT;
+            if (p < pairs) {
+                const size_t at = pair_at(p);
+                xy[q] = __ldg(src + 2 * at); zm[q] = __ldg(src + 2 * at + 1);
+            } else {   // zero-mass pair at the origin contributes exactly +0 (eps2 > 0)
+                xy[q] = make_ulonglong2(0ull, 0ull); zm[q] = make_ulonglong2(0ull, 0ull);
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < UNROLL; ++q) {
+#pragma unroll
+            for (int t = 0; t < TT; ++t) {
+                const u64 dx = add2(xy[q].x, nx[t]), dy = add2(xy[q].y, ny[t]), dz = add2(zm[q].x, nz[t]);
+                u64 r2 = fma2(dx, dx, eps2p);
+                r2 = fma2(dy, dy, r2);
+                r2 = fma2(dz, dz, r2);
+                const u64 d3 = mul2(mul2(r2, r2), r2);
+                float lo, hi;
+                unpack2(d3, lo, hi);
+                const u64 sc = mul2(pack2(rsqrt_mufu(lo), rsqrt_mufu(hi)), zm[q].y);
+                ax[t] = fma2(dx, sc, ax[t]);
+                ay[t] = fma2(dy, sc, ay[t]);
+                az[t] = fma2(dz, sc, az[t]);
+            }
+        }
+    }
+    // ---- reduce the NT partial sums of every target: lanes (shfl.xor), then warps (smem) ----------
+#pragma unroll
+    for (int t = 0; t < TT; ++t) {
+        float lo, hi, f[3];
+        unpack2(ax[t], lo, hi); f[0] = lo + hi;
+        unpack2(ay[t], lo, hi); f[1] = lo + hi;
+        unpack2(az[t], lo, hi); f[2] = lo + hi;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+#pragma unroll
+            for (int m = 16; m > 0; m >>= 1) f[c] = __fadd_rn(f[c], __shfl_xor_sync(0xffffffffu, f[c], m));
+            if (lane == 0) s_part[wid][3 * t + c] = f[c];
+        }
+    }
+    __syncthreads();
+    if (wid == 0) {
+        float fx = 0.f, fy = 0.f, fz = 0.f;
+        if (lane < TT) {
+#pragma unroll
+            for (int w = 0; w < NW; ++w) {
+                fx = __fadd_rn(fx, s_part[w][3 * lane]); fy = __fadd_rn(fy, s_part[w][3 * lane + 1]); fz = __fadd_rn(fz, s_part[w][3 * lane + 2]);
+            }
+        }
+        const int gi = g0 + lane;
+        integrate_one(a, gi, lane < TT && gi < a.n_targets, fx, fy, fz, lane);
+    }
+}
+
 // ---- AoS float4 -> packed pair layout (pre-pass of the in-place API and of upload) ----
 // Covers bodies [0, n_cover) of the destination starting at packed body index
 // `off` (even); bodies >= n are written as zero-mass padding.
