@@ -266,6 +266,10 @@ struct nbody_ctx {
     unsigned char* frame = nullptr;              // nbody_render's device RGBA8 frame
     size_t frame_bytes = 0;
     long long steps_done = 0;                    // full steps since the last upload / snapshot load
+    // launch-bound step loops (small N): kGraphSteps consecutive steps captured once as a CUDA graph
+    // (buffer parity 0 at entry); replayed by nbody_step_async
+    cudaGraphExec_t step_graph = nullptr;
+    bool graph_failed = false;
     // fused exchange: peers' packed buffers [peer rank][0/1]; ipc = opened with cudaIpcOpenMemHandle
     float4* peer_packed[kMaxPeers + 1][2] = {};
     bool peer_ipc[kMaxPeers + 1] = {};
@@ -351,6 +355,7 @@ void nbody_destroy(nbody_ctx* c)
     cudaSetDevice(c->p.device);
     for (int r = 0; r <= kMaxPeers; ++r)
         if (c->peer_ipc[r]) { cudaIpcCloseMemHandle(c->peer_packed[r][0]); cudaIpcCloseMemHandle(c->peer_packed[r][1]); }
+    if (c->step_graph) cudaGraphExecDestroy(c->step_graph);
     cudaFree(c->X); cudaFree(c->V); cudaFree(c->A); cudaFree(c->accum);
     cudaFree(c->packed[0]); cudaFree(c->packed[1]);
     cudaFree(c->partial); cudaFree(c->counters); cudaFree(c->energy_part); cudaFree(c->stage); cudaFree(c->frame);

@@ -19,6 +19,37 @@ int enqueue_full_step(nbody_ctx* c, cudaStream_t st)
     return NBODY_OK;
 }
 
+// A step of a few microseconds is bound by launch latency, not by the kernel: replay kGraphSteps
+// steps as one CUDA graph.  Captured lazily, once per context, with buffer parity 0 at entry
+// (kGraphSteps is even, so parity is 0 again at exit).  Returns false when capture is not possible;
+// the caller then launches step by step.
+constexpr int kGraphSteps = 32;
+constexpr int kGraphMaxBodies = 16384;   // above this a step is > 100 us and launches hide behind it
+
+bool ensure_step_graph(nbody_ctx* c)
+{
+    if (c->step_graph) return true;
+    if (c->graph_failed || c->p.world != 1 || c->n > kGraphMaxBodies || c->cur != 0) return false;
+    cudaGraph_t g = nullptr;
+    if (cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { c->graph_failed = true; cudaGetLastError(); return false; }
+    bool ok = true;
+    const long long steps0 = c->steps_done;
+    for (int s = 0; s < kGraphSteps && ok; ++s) ok = enqueue_full_step(c, c->stream) == NBODY_OK;
+    const cudaError_t e = cudaStreamEndCapture(c->stream, &g);
+    c->steps_done = steps0;          // nothing ran yet
+    c->cur = 0;                      // kGraphSteps is even
+    g_launches.fetch_sub(ok ? kGraphSteps : 0, std::memory_order_relaxed);
+    if (ok && e == cudaSuccess && cudaGraphInstantiate(&c->step_graph, g, 0) == cudaSuccess) {
+        cudaGraphDestroy(g);
+        return true;
+    }
+    if (g) cudaGraphDestroy(g);
+    cudaGetLastError();
+    c->step_graph = nullptr;
+    c->graph_failed = true;
+    return false;
+}
+
 }  // namespace
 
 extern "C" {
@@ -73,7 +104,22 @@ int nbody_step_async(nbody_ctx* c, int nsteps)
     int rc = set_device(c);
     if (rc) return rc;
     CU(cudaEventRecord(c->ev0, c->stream));
-    for (int s = 0; s < nsteps; ++s) {
+    int s = 0;
+    if (nsteps >= kGraphSteps + 1 && c->n <= kGraphMaxBodies && !c->graph_failed) {
+        if (c->cur != 0) {           // graphs start from buffer parity 0
+            rc = enqueue_full_step(c, c->stream);
+            if (rc) return rc;
+            ++s;
+        }
+        if (ensure_step_graph(c)) {
+            for (; s + kGraphSteps <= nsteps; s += kGraphSteps) {
+                CU(cudaGraphLaunch(c->step_graph, c->stream));
+                g_launches.fetch_add(kGraphSteps, std::memory_order_relaxed);   // kernels run, not API calls
+                c->steps_done += kGraphSteps;
+            }
+        }
+    }
+    for (; s < nsteps; ++s) {
         rc = enqueue_full_step(c, c->stream);
         if (rc) return rc;
     }

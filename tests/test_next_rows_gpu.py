@@ -213,3 +213,22 @@ def test_fused_exchange_on_one_gpu_matches_unsharded(cuda, nb, oracle, world):
     x = np.concatenate([p[0] for p in parts]); v = np.concatenate([p[1] for p in parts]); a = np.concatenate([p[2] for p in parts])
     # same kernel, same source order per target tile only when the stream-K cut coincides: compare to rounding
     assert oracle.norm_rel_err(a, ar) <= 3e-6 and oracle.norm_rel_err(x, xr) <= 1e-6 and oracle.norm_rel_err(v, vr) <= 3e-6
+
+
+# ---- launch-bound step loops: CUDA-graph replay gives the same bits as step-by-step launches ---------------
+@pytest.mark.parametrize("n", [777, 5000])
+def test_graph_replayed_steps_equal_single_steps(cuda, nb, n):
+    x0, v0 = nb.ic_plummer(n, seed=8)
+    with nb.Simulation(n, dt=0.01) as sim:
+        sim.upload(x0, v0)
+        for _ in range(71):
+            sim.step(1)                                        # 71 separate launches
+        one_by_one = sim.download()
+    with nb.Simulation(n, dt=0.01) as sim:
+        sim.upload(x0, v0).step(3)                             # leaves buffer parity 1: replay must realign
+        before = nb.launch_count()
+        sim.step(68)                                           # 1 single + 2 x 32 replayed + 3 single
+        assert nb.launch_count() - before == 68 and sim.steps_done() == 71
+        replayed = sim.download()
+    for a, b in zip(one_by_one, replayed):
+        assert np.array_equal(a, b)
