@@ -44,6 +44,9 @@ def parse():
     ap.add_argument("--exchange", default="p2p", choices=["nccl", "p2p"],
                     help="multi-GPU position exchange: P2P stores fused into the step's epilogue (default; r1: +0.3%% at N=1M, "
                          "+4.4%% at N=256k on 8 GPUs), or an NCCL all-gather overlapped with the own-slice kernel")
+    ap.add_argument("--cpu-series", action="store_true",
+                    help="with --impl reference: also print baseline B1 of BASELINE.md (reference CPU path at N=1024x10, 16384x3, "
+                         "131072x1, -O2 and -O3 builds) as extra JSON lines BEFORE the contract line")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -151,10 +154,33 @@ def cpu_reference_rate(n, steps, warmup):
     return n * float(n) / dt / 1e9, kind, o.num_threads(), dt
 
 
+def cpu_series():
+    """baseline B1: the reference's CPU_compute at its three CPU-runnable configs"""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import numpy as np
+    import oracle as o
+    for build, flags in ((True, "-O2 -fopenmp"), ("o3", "-O3 -march=x86-64-v3 -fopenmp")):
+        if o.ref_lib(build) is None:
+            continue
+        for n, steps in ((1024, 10), (16384, 3), (131072, 1)):
+            x = o.ic_reference(n)
+            v, a = np.zeros_like(x), np.zeros_like(x)
+            o.ref_cpu_compute(x, a, v, omp=build)            # warm-up (thread pool, page faults)
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                o.ref_cpu_compute(x, a, v, omp=build)
+            dt = (time.perf_counter() - t0) / steps
+            print(json.dumps({"baseline": "B1 reference CPU_compute (validation.cpp:28-52)", "build": flags, "n": n, "steps": steps,
+                              "threads": o.num_threads(), "ms_per_step": round(dt * 1e3, 3),
+                              "g_inter_per_s": round(n * float(n) / dt / 1e9, 3)}), flush=True)
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    if args.cpu_series:
+        cpu_series()
     n = 32768   # bounded sample: ~1 s per step on 8 cores; throughput is N-independent at this size
     rate, kind, cores, dt = cpu_reference_rate(n, args.steps, min(args.warmup, 1))
     sample = f"CPU_compute (validation.cpp:28-52, OpenMP pragma on) over {n} bodies per step ({n * n:.3g} interactions), {cores} threads"

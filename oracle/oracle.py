@@ -99,8 +99,9 @@ def verify_still_bodies(v, x) -> int:
 
 
 # ---- the reference's own object code (present only when oracle/_ref was built) ----------
-def ref_lib(omp: bool = False):
-    p = os.path.join(HERE, "_ref", "libref_cpu_omp.so" if omp else "libref_cpu.so")
+def ref_lib(omp=False):
+    """omp: False = serial build (as the vcxproj), True = -O2 -fopenmp, "o3" = -O3 -march=x86-64-v3 -fopenmp"""
+    p = os.path.join(HERE, "_ref", "libref_cpu_omp_o3.so" if omp == "o3" else "libref_cpu_omp.so" if omp else "libref_cpu.so")
     return C.CDLL(p) if os.path.exists(p) else None
 
 
