@@ -13,11 +13,14 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import nbody_b200 as nb  # noqa: E402  (only for the seeded ICs)
 
-lib = C.CDLL(os.path.join(ROOT, "oracle", "_ref", "libref_kernel_sm100.so"))
+retuned = len(sys.argv) > 1 and sys.argv[1] == "tpb256"
+label = ("reference kernel.cu rebuilt for sm_100, RE-TUNED to THREADS_PER_BLOCK 256 (not as shipped)" if retuned
+         else "reference kernel.cu rebuilt for sm_100 (32x1 launch as shipped)")
+lib = C.CDLL(os.path.join(ROOT, "oracle", "_ref", "libref_kernel_sm100_tpb256.so" if retuned else "libref_kernel_sm100.so"))
 simulate = getattr(lib, "_Z8simulateP6float4S0_S0_i")
 simulate.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
 simulate.restype = None
-for n, steps in ((16384, 20), (131072, 3), (1 << 20, 1), (8388608, 1)):
+for n, steps in ((16384, 20), (131072, 3), (1 << 20, 1)) + (() if retuned else ((8388608, 1),)):
     x = torch.from_numpy(nb.ic_uniform(n, seed=12345)).cuda()
     v, a = torch.zeros_like(x), torch.zeros_like(x)
     try:
@@ -30,7 +33,7 @@ for n, steps in ((16384, 20), (131072, 3), (1 << 20, 1), (8388608, 1)):
         e1.record()
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / steps
-        print(json.dumps({"baseline": "reference kernel.cu rebuilt for sm_100 (32x1 launch as shipped)", "n": n, "ms_per_step": round(ms, 3),
+        print(json.dumps({"baseline": label, "n": n, "ms_per_step": round(ms, 3),
                           "g_inter_per_s": round(n * float(n) / ms / 1e6, 2)}), flush=True)
     except Exception as e:  # noqa: BLE001  (the launcher throws via C++; through ctypes that aborts -- see note)
         print(json.dumps({"n": n, "error": str(e)}), flush=True)
