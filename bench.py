@@ -47,6 +47,9 @@ def parse():
     ap.add_argument("--cpu-series", action="store_true",
                     help="with --impl reference: also print baseline B1 of BASELINE.md (reference CPU path at N=1024x10, 16384x3, "
                          "131072x1, -O2 and -O3 builds) as extra JSON lines BEFORE the contract line")
+    ap.add_argument("--ref-kernel-series", action="store_true",
+                    help="with --impl reference: also print baseline B2 of BASELINE.md (the reference's kernel.cu rebuilt for sm_100, "
+                         "oracle/_ref/libref_kernel_sm100*.so, as shipped and re-tuned to 256 threads) as extra JSON lines; needs a GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -175,12 +178,49 @@ def cpu_series():
                               "g_inter_per_s": round(n * float(n) / dt / 1e9, 3)}), flush=True)
 
 
+def ref_kernel_series():
+    """baseline B2: the reference's own kernel.cu rebuilt for sm_100 (one-token fix at
+    kernel.cu:99, nvcc -O3, no fast-math; see oracle/Makefile), timed with CUDA events around its own simulate()
+    (kernel.cu:628-645).  A reported baseline; none of our kernels run here."""
+    import ctypes as C
+    import torch
+    import nbody_b200 as nb   # seeded ICs only
+    for so, label, sizes in (
+            ("libref_kernel_sm100.so", "B2 reference kernel.cu rebuilt for sm_100 (THREADS_PER_BLOCK 32 as shipped)",
+             ((16384, 20), (131072, 3), (1 << 20, 1))),
+            ("libref_kernel_sm100_tpb256.so", "B2' reference kernel.cu, RE-TUNED to THREADS_PER_BLOCK 256 (not as shipped)",
+             ((16384, 20), (131072, 3), (1 << 20, 1)))):
+        path = os.path.join(ROOT, "oracle", "_ref", so)
+        if not os.path.exists(path):
+            continue
+        sim = getattr(C.CDLL(path), "_Z8simulateP6float4S0_S0_i")
+        sim.argtypes, sim.restype = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int], None
+        for n, steps in sizes:
+            x = torch.from_numpy(nb.ic_uniform(n, seed=12345)).cuda()
+            v, a = torch.zeros_like(x), torch.zeros_like(x)
+            if n <= 131072:
+                sim(x.data_ptr(), a.data_ptr(), v.data_ptr(), n)   # warm-up
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                sim(x.data_ptr(), a.data_ptr(), v.data_ptr(), n)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / steps
+            print(json.dumps({"baseline": label, "n": n, "ms_per_step": round(ms, 3), "g_inter_per_s": round(n * float(n) / ms / 1e6, 2)}), flush=True)
+    print(json.dumps({"baseline": "B2 reference kernel.cu rebuilt for sm_100", "n": 8388608,
+                      "error": "the reference's launcher throws \"Shared memory request too large.\" (kernel.cu:639-641): 16*N B > 228 KiB x 148 SMs; "
+                               "not called here (a C++ exception through ctypes aborts the process); a guard-bypassed run would take ~100 s per step"}), flush=True)
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     if args.cpu_series:
         cpu_series()
+    if args.ref_kernel_series:
+        ref_kernel_series()
     n = 32768   # bounded sample: ~1 s per step on 8 cores; throughput is N-independent at this size
     rate, kind, cores, dt = cpu_reference_rate(n, args.steps, min(args.warmup, 1))
     sample = f"CPU_compute (validation.cpp:28-52, OpenMP pragma on) over {n} bodies per step ({n * n:.3g} interactions), {cores} threads"

@@ -118,6 +118,12 @@ const Variant kVariants[] = {
     VARIANT(50, 6, 256, 512, 2, 4, 1),
     VARIANT(51, 4, 256, 256, 4, 4, 2),
     VARIANT(52, 6, 256, 256, 1, 4, 1),
+    VARIANT(53, 7, 256, 256, 2, 1, 1),
+    VARIANT(54, 4, 384, 256, 4, 1, 1),
+    VARIANT(55, 5, 384, 256, 2, 1, 1),
+    VARIANT(56, 6, 384, 256, 2, 1, 1),
+    VARIANT(57, 3, 512, 256, 4, 1, 1),
+    VARIANT(58, 4, 384, 256, 2, 1, 1),
     // thread-block-cluster variants: m1 = TMA multicast, m2 = j-split with DSMEM reduction
     CVARIANT(60, 6, 256, 256, 2, 1, 1, 2, 1),
     CVARIANT(61, 6, 256, 256, 2, 1, 1, 4, 1),

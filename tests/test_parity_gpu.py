@@ -208,3 +208,34 @@ def test_sharded_contexts_on_one_gpu_match_unsharded(cuda, nb, oracle, world):
     x = np.concatenate([p[0] for p in parts]); v = np.concatenate([p[1] for p in parts]); a = np.concatenate([p[2] for p in parts])
     assert len(x) == n
     assert oracle.norm_rel_err(a, ar) <= 3e-6 and oracle.norm_rel_err(x, xr) <= 1e-6 and oracle.norm_rel_err(v, vr) <= 3e-6
+
+
+def _problem_counts(binary, steps):
+    """lines printed by the reference's verify_still_bodies (validation.cpp:143-164) per array"""
+    import subprocess
+    out = subprocess.run([binary, str(steps)], capture_output=True, text=True, timeout=300, check=True).stdout
+    counts, sec = {}, None
+    for line in out.splitlines():
+        if line.startswith("=="):
+            sec = line.split()[1]
+            counts.setdefault(sec, 0)
+        elif line.startswith("Problem at body") and sec:
+            counts[sec] += 1
+    return counts
+
+
+def test_reference_checker_objects_accept_our_simulate_as_they_accept_their_own_kernel(cuda):
+    # oracle/_ref/ref_validate      : reference validation.cpp + utils.cpp objects (unmodified) + OUR simulate()
+    # oracle/_ref/ref_validate_self : the same objects + the reference's own kernel.cu (sm_100 rebuild)
+    # after K lock-stepped steps the reference's own 1 % check must flag no more bodies with our engine than with
+    # the reference's kernel (its CPU side updates positions in place, SURVEY F4, so neither can reach zero)
+    import os
+    ref = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref")
+    ours, own = os.path.join(ref, "ref_validate"), os.path.join(ref, "ref_validate_self")
+    if not (os.path.exists(ours) and os.path.exists(own)):
+        pytest.skip("oracle/_ref binaries were not built (they need /root/reference at build time)")
+    for steps in (1, 10):
+        a, b = _problem_counts(ours, steps), _problem_counts(own, steps)
+        assert a["positions"] <= b["positions"] + 2, (steps, a, b)
+        assert a["velocities"] <= 1.1 * b["velocities"] + 2 and a["accelerations"] <= 1.1 * b["accelerations"] + 2, (steps, a, b)
+    assert a["positions"] < 0.01 * 8192                      # 10 steps: > 99 % of the bodies within the reference's own 1 %
