@@ -270,6 +270,7 @@ struct nbody_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timed = false;
     unsigned char* frame = nullptr;              // nbody_render's device RGBA8 frame
+    unsigned long long* frame_keys = nullptr;    // per-pixel depth|index keys of that frame
     size_t frame_bytes = 0;
     long long steps_done = 0;                    // full steps since the last upload / snapshot load
     // launch-bound step loops (small N): kGraphSteps consecutive steps captured once as a CUDA graph
@@ -364,7 +365,7 @@ void nbody_destroy(nbody_ctx* c)
     if (c->step_graph) cudaGraphExecDestroy(c->step_graph);
     cudaFree(c->X); cudaFree(c->V); cudaFree(c->A); cudaFree(c->accum);
     cudaFree(c->packed[0]); cudaFree(c->packed[1]);
-    cudaFree(c->partial); cudaFree(c->counters); cudaFree(c->energy_part); cudaFree(c->stage); cudaFree(c->frame);
+    cudaFree(c->partial); cudaFree(c->counters); cudaFree(c->energy_part); cudaFree(c->stage); cudaFree(c->frame); cudaFree(c->frame_keys);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);

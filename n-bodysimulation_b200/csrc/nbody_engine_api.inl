@@ -316,6 +316,7 @@ struct Cached {
     float4 *X = nullptr, *V = nullptr, *A = nullptr;   // host-pointer flavour only
     int n_pad = 0;
 };
+void release_render_scratch();   // nbody_render.inl
 std::mutex g_cache_mu;
 std::map<std::pair<std::pair<int, int>, int>, Cached> g_cache;   // ((device, N), variant)
 
@@ -448,6 +449,7 @@ void nbody_release_cached(void)
         free_cached(kv.second);
     }
     g_cache.clear();
+    release_render_scratch();
     cudaSetDevice(cur);
 }
 

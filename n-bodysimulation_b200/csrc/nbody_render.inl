@@ -88,27 +88,33 @@ __global__ void render_resolve_kernel(const float4* __restrict__ X, ViewArgs v, 
 std::mutex g_render_mu;
 std::map<int, std::pair<unsigned long long*, size_t>> g_render_keys;   // device -> (keys, pixels)
 
-int render_on_device(const float4* dX, int n, const nbody_view* v, unsigned char* d_rgba, cudaStream_t st)
+void release_render_scratch()
 {
-    if (!dX || !v || !d_rgba) return fail(NBODY_E_INVALID, "null argument");
-    if (n <= 0) return fail(NBODY_E_INVALID, "N must be > 0 (got %d)", n);
+    std::lock_guard<std::mutex> lk(g_render_mu);
+    for (auto& kv : g_render_keys) {
+        cudaSetDevice(kv.first);
+        cudaFree(kv.second.first);
+    }
+    g_render_keys.clear();
+}
+
+int check_view(const nbody_view* v)
+{
+    if (!v) return fail(NBODY_E_INVALID, "null view");
     if (v->width <= 0 || v->height <= 0 || (long long)v->width * v->height > (1ll << 28)) return fail(NBODY_E_INVALID, "bad frame size %dx%d", v->width, v->height);
     if (!(v->max_x > 0.f && v->max_y > 0.f && v->max_z > 0.f) || !(v->max_w > v->min_w)) return fail(NBODY_E_INVALID, "bad view volume / weight range");
+    return NBODY_OK;
+}
+
+// enqueue clear + splat + resolve on `st`; `keys` holds width*height 64-bit words and must not be
+// shared with another frame in flight
+int render_on_device(const float4* dX, int n, const nbody_view* v, unsigned long long* keys, unsigned char* d_rgba, cudaStream_t st)
+{
     const int npix = v->width * v->height;
-    int dev = 0;
-    CU(cudaGetDevice(&dev));
-    std::lock_guard<std::mutex> lk(g_render_mu);
-    auto& kb = g_render_keys[dev];
-    if (kb.second < (size_t)npix) {
-        cudaFree(kb.first);
-        kb = std::make_pair((unsigned long long*)nullptr, (size_t)0);
-        CU(cudaMalloc(&kb.first, (size_t)npix * sizeof(unsigned long long)));
-        kb.second = (size_t)npix;
-    }
     ViewArgs a{v->width, v->height, v->max_x, v->max_y, v->max_z, v->min_w, v->max_w, v->depth_test ? 1 : 0};
-    render_clear_kernel<<<(npix + 255) / 256, 256, 0, st>>>(kb.first, npix, a.depth_test);
-    render_splat_kernel<<<(n + 255) / 256, 256, 0, st>>>(dX, n, a, kb.first);
-    render_resolve_kernel<<<(npix + 255) / 256, 256, 0, st>>>(dX, a, kb.first, reinterpret_cast<uchar4*>(d_rgba));
+    render_clear_kernel<<<(npix + 255) / 256, 256, 0, st>>>(keys, npix, a.depth_test);
+    render_splat_kernel<<<(n + 255) / 256, 256, 0, st>>>(dX, n, a, keys);
+    render_resolve_kernel<<<(npix + 255) / 256, 256, 0, st>>>(dX, a, keys, reinterpret_cast<uchar4*>(d_rgba));
     g_launches.fetch_add(3, std::memory_order_relaxed);
     CU(cudaGetLastError());
     return NBODY_OK;
@@ -130,7 +136,22 @@ int nbody_view_default(nbody_view* v)
 
 int nbody_render_device(const float* d_bodies4, int n, const nbody_view* v, unsigned char* d_rgba)
 {
-    int rc = render_on_device(reinterpret_cast<const float4*>(d_bodies4), n, v, d_rgba, 0);
+    if (!d_bodies4 || !d_rgba) return fail(NBODY_E_INVALID, "null argument");
+    if (n <= 0) return fail(NBODY_E_INVALID, "N must be > 0 (got %d)", n);
+    int rc = check_view(v);
+    if (rc) return rc;
+    const size_t npix = (size_t)v->width * v->height;
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(g_render_mu);   // held until the frame is finished: the per-device keys are shared
+    auto& kb = g_render_keys[dev];
+    if (kb.second < npix) {
+        cudaFree(kb.first);
+        kb = std::make_pair((unsigned long long*)nullptr, (size_t)0);
+        CU(cudaMalloc(&kb.first, npix * sizeof(unsigned long long)));
+        kb.second = npix;
+    }
+    rc = render_on_device(reinterpret_cast<const float4*>(d_bodies4), n, v, kb.first, d_rgba, 0);
     if (rc) return rc;
     CU(cudaDeviceSynchronize());
     return NBODY_OK;
@@ -138,19 +159,21 @@ int nbody_render_device(const float* d_bodies4, int n, const nbody_view* v, unsi
 
 int nbody_render(nbody_ctx* c, const nbody_view* v, unsigned char* h_rgba)
 {
-    if (!c || !v || !h_rgba) return fail(NBODY_E_INVALID, "null argument");
-    if (c->p.world != 1) return fail(NBODY_E_STATE, "nbody_render needs an unsharded context (each shard holds only its own bodies' masses in order)");
-    int rc = set_device(c);
+    if (!c || !h_rgba) return fail(NBODY_E_INVALID, "null argument");
+    if (c->p.world != 1) return fail(NBODY_E_STATE, "nbody_render needs an unsharded context (a shard holds only its own bodies)");
+    int rc = check_view(v);
     if (rc) return rc;
-    const size_t bytes = (size_t)v->width * v->height * 4;
-    if (v->width <= 0 || v->height <= 0) return fail(NBODY_E_INVALID, "bad frame size %dx%d", v->width, v->height);
-    if (c->frame_bytes < bytes) {
-        cudaFree(c->frame);
-        c->frame = nullptr; c->frame_bytes = 0;
+    rc = set_device(c);
+    if (rc) return rc;
+    const size_t npix = (size_t)v->width * v->height, bytes = npix * 4;
+    if (c->frame_bytes < bytes) {   // frame + its keys live with the context (its stream orders their use)
+        cudaFree(c->frame); cudaFree(c->frame_keys);
+        c->frame = nullptr; c->frame_keys = nullptr; c->frame_bytes = 0;
         CU(cudaMalloc(&c->frame, bytes));
+        CU(cudaMalloc(&c->frame_keys, npix * sizeof(unsigned long long)));
         c->frame_bytes = bytes;
     }
-    rc = render_on_device(c->X, c->n, v, c->frame, c->stream);
+    rc = render_on_device(c->X, c->n, v, c->frame_keys, c->frame, c->stream);
     if (rc) return rc;
     CU(cudaMemcpyAsync(h_rgba, c->frame, bytes, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
