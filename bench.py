@@ -92,7 +92,7 @@ def peaks():
 # ---- clocks during the timed region ----------------------------------------------------------
 class ClockSampler:
     def __init__(self, index=0, period=0.1):
-        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self.samples, self.reasons, self.max_mhz, self.power = [], set(), None, []
         self._stop = threading.Event()
         self._t = None
         self.index, self.period = index, period
@@ -112,6 +112,10 @@ class ClockSampler:
         while not self._stop.is_set():
             try:
                 self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    self.power.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
+                except Exception:  # noqa: BLE001
+                    pass
                 r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
                 for k, bit in names.items():
                     if r & bit:
@@ -133,7 +137,10 @@ class ClockSampler:
 
     def summary(self):
         s = sorted(self.samples)
-        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "samples": len(s), "reasons": sorted(self.reasons)}
+        out = {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "samples": len(s), "reasons": sorted(self.reasons)}
+        if self.power:
+            out["power_w_max"] = round(max(self.power), 1)
+        return out
 
 
 # ---- reference arm / cpu baseline ------------------------------------------------------------------
@@ -363,6 +370,12 @@ def run_ours(args):
             "kernel": info["variant_name"], "launches_per_step": launches / K}
     if clocks["sm_mhz"]:
         roof["frac_at_sampled_clock"] = round(achieved / (sms * 128 * 2 * clocks["sm_mhz"] * 1e6 / 1e12), 4)
+    try:   # clock64 / globaltimer inside the last timed kernel: the clock the SMs really delivered
+        mhz = sim.kernel_clock_mhz()
+        clocks["sm_mhz_in_kernel"] = round(mhz, 1)
+        roof["frac_at_in_kernel_clock"] = round(achieved / (sms * 128 * 2 * mhz * 1e6 / 1e12), 4)
+    except Exception:  # noqa: BLE001  (small-N family kernels do not record it)
+        pass
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -378,7 +391,7 @@ def run_ours(args):
                 "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
                 "pct_fp32_peak": round(100 * achieved / peak_tflops, 2),
                 "engine": {"variant": info["variant_name"], "grid_ctas": info["grid_ctas"], "ctas_per_sm": info["ctas_per_sm"],
-                           "exchange": exchange}}
+                           "exchange": exchange, "autotune": nb.autotune_report()}}
         print(json.dumps(line), flush=True)
     sim.close()
     if world > 1:

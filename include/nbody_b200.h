@@ -94,6 +94,12 @@ int nbody_sync(nbody_ctx* ctx);
  * events on the context's stream).  The reference has no timing. */
 int nbody_elapsed_ms(nbody_ctx* ctx, float* ms);
 
+/* SM clock the last stream-K force kernel of this context actually ran at: cycles
+ * (clock64) over wall time (globaltimer) between entry and exit of its first CTA.
+ * NVML reports the requested clock; under a sustained FP32 load the delivered one
+ * is a few per cent lower on some boards (SURVEY section 8d asks for both). */
+int nbody_kernel_clock_mhz(nbody_ctx* ctx, float* mhz);
+
 /* Kinetic energy and pair potential sum_{i<j} -m_i m_j/sqrt(r^2+eps2) of the
  * current state, accumulated in double on the device (unsharded contexts).
  * The scheme's conserved quantity is ke + 0.5*pe. */
@@ -200,6 +206,12 @@ long long nbody_launch_count(void);
  * number of variants.  nbody_variant_id(i), i = 0..count-1, lists the ids. */
 int nbody_variant_info(int id, char* buf, size_t buflen);
 int nbody_variant_id(int index);
+/* "id:ms id:ms ..." of the large-N candidates timed when the first large context of
+ * this process resolved NBODY_VARIANT_AUTO (empty before that).  The candidates run the
+ * same instructions per interaction in different source order; which register
+ * allocation ptxas gave each is worth +-3.5 %, so the engine measures instead of
+ * guessing.  Environment NBODY_LARGE_VARIANT=<id> forces the choice. */
+int nbody_autotune_report(char* buf, size_t buflen);
 /* Variant / grid actually used by ctx (after AUTO resolution). */
 int nbody_ctx_info(nbody_ctx* ctx, int* variant, int* grid_ctas, int* ctas_per_sm, int* sm_count);
 

@@ -63,6 +63,7 @@ SIGNATURES = {
     "nbody_step_async": (C.c_int, [_vp, C.c_int]),
     "nbody_sync": (C.c_int, [_vp]),
     "nbody_elapsed_ms": (C.c_int, [_vp, C.POINTER(C.c_float)]),
+    "nbody_kernel_clock_mhz": (C.c_int, [_vp, C.POINTER(C.c_float)]),
     "nbody_energy": (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "nbody_shard_local_async": (C.c_int, [_vp, _vp]),
     "nbody_shard_remote_async": (C.c_int, [_vp, _vp]),
@@ -90,6 +91,7 @@ SIGNATURES = {
     "nbody_launch_count": (C.c_longlong, []),
     "nbody_variant_info": (C.c_int, [C.c_int, C.c_char_p, C.c_size_t]),
     "nbody_variant_id": (C.c_int, [C.c_int]),
+    "nbody_autotune_report": (C.c_int, [C.c_char_p, C.c_size_t]),
     "nbody_ctx_info": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "nbody_ic_uniform": (C.c_int, [_vp, C.c_int, C.c_ulonglong, C.c_float, C.c_float, C.c_float]),
     "nbody_ic_plummer": (C.c_int, [_vp, _vp, C.c_int, C.c_ulonglong]),
@@ -133,6 +135,12 @@ def variants() -> dict:
         lib.nbody_variant_info(i, buf, 320)
         out[i] = buf.value.decode()
     return out
+
+
+def autotune_report() -> str:
+    buf = C.create_string_buffer(512)
+    _check(lib.nbody_autotune_report(buf, 512))
+    return buf.value.decode()
 
 
 # ---- the reference's launch interface ------------------------------------------------
@@ -281,6 +289,11 @@ class Simulation:
         a = np.empty((self.count, 4), np.float32)
         _check(lib.nbody_download(self._h, _ptr(x), _ptr(v), _ptr(a)))
         return x, v, a
+
+    def kernel_clock_mhz(self) -> float:
+        mhz = C.c_float()
+        _check(lib.nbody_kernel_clock_mhz(self._h, C.byref(mhz)))
+        return mhz.value
 
     def energy(self):
         ke, pe = C.c_double(), C.c_double()

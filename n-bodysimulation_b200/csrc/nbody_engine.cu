@@ -9,6 +9,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -124,6 +125,13 @@ const Variant kVariants[] = {
     VARIANT(56, 6, 384, 256, 2, 1, 1),
     VARIANT(57, 3, 512, 256, 4, 1, 1),
     VARIANT(58, 4, 384, 256, 2, 1, 1),
+    VARIANT(90, 6, 256, 256, 2, 5, 1),
+    VARIANT(91, 6, 256, 256, 2, 6, 1),
+    VARIANT(92, 8, 256, 256, 2, 5, 1),
+    VARIANT(93, 8, 256, 256, 2, 6, 1),
+    VARIANT(94, 7, 256, 256, 2, 6, 1),
+    VARIANT(95, 6, 256, 256, 4, 6, 1),
+    VARIANT(96, 8, 256, 512, 2, 6, 1),
     // thread-block-cluster variants: m1 = TMA multicast, m2 = j-split with DSMEM reduction
     CVARIANT(60, 6, 256, 256, 2, 1, 1, 2, 1),
     CVARIANT(61, 6, 256, 256, 2, 1, 1, 4, 1),
@@ -155,6 +163,8 @@ const Variant* find_variant(int id)
     return nullptr;
 }
 
+int tuned_large_variant();
+
 int auto_variant(int n_targets, int n_sources)
 {
     // best of the r1 sweeps (profiles/r1_variant_sweep_*.jsonl); the cluster variants (60-70)
@@ -163,7 +173,7 @@ int auto_variant(int n_targets, int n_sources)
         if (n_sources < 3072) return 85; // 2 targets / CTA, sources split over 128 threads, shuffle reduction
         return 82;                       // 4 targets / CTA
     }
-    if (n_targets >= 12288) return 45;   // T6 x 256 threads, 1 CTA/SM
+    if (n_targets >= 12288) return tuned_large_variant();   // T6/T8 x 256 threads, 1 CTA/SM: picked by measurement
     if (n_targets >= 2048) return 3;     // T2 x 256 threads, 3 CTAs/SM
     return 12;                           // T1 x 128 threads, 64-body units
 }
@@ -249,6 +259,82 @@ int launch_pack(const float4* X, int n, float4* packed, int off, int n_cover, cu
     return NBODY_OK;
 }
 
+// ---- which of the equivalent large-N kernels is fastest on this device ---------------------------------
+// Variants 45/90/91 (T6) and 21/92/93/96 (T8) issue the same instructions per interaction and differ
+// only in source order, i.e. in the register allocation ptxas happens to give them; measured, that is
+// worth +-3.5 % (register-bank conflicts on the 3-operand FFMA2; profiles/r1_variant_sweep_*).  Rather
+// than trust one allocation, the first large context of a process times each candidate for ~1 ms on
+// synthetic bodies and keeps the fastest (NBODY_LARGE_VARIANT=<id> in the environment overrides).
+const int kTuneCandidates[] = {45, 90, 91, 21, 92, 93, 96};
+constexpr int kTuneBodies = 49152;   // whole tiles for T6 (1536) and T8 (2048): 0.9 ms per launch
+std::mutex g_tune_mu;
+std::map<int, int> g_tuned;          // device -> variant id
+std::string g_tune_report;
+
+int tuned_large_variant()
+{
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 45;
+    std::lock_guard<std::mutex> lk(g_tune_mu);
+    auto it = g_tuned.find(dev);
+    if (it != g_tuned.end()) return it->second;
+    int best = 45;
+    if (const char* env = getenv("NBODY_LARGE_VARIANT")) {
+        const int id = atoi(env);
+        if (find_variant(id) && !find_variant(id)->small) { g_tuned[dev] = id; g_tune_report = "forced by NBODY_LARGE_VARIANT"; return id; }
+    }
+    cudaDeviceProp prop;
+    float4 *X = nullptr, *V = nullptr, *A = nullptr, *src = nullptr, *partial = nullptr;
+    unsigned* counters = nullptr;
+    cudaStream_t st = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    const size_t nb = (size_t)kTuneBodies * sizeof(float4);
+    bool ok = cudaGetDeviceProperties(&prop, dev) == cudaSuccess && cudaMalloc(&X, nb) == cudaSuccess && cudaMalloc(&V, nb) == cudaSuccess &&
+              cudaMalloc(&A, nb) == cudaSuccess && cudaMalloc(&src, nb) == cudaSuccess && cudaMalloc(&counters, 4096) == cudaSuccess &&
+              cudaMemset(X, 0, nb) == cudaSuccess && cudaMemset(V, 0, nb) == cudaSuccess && cudaMemset(src, 0, nb) == cudaSuccess &&
+              cudaMemset(counters, 0, 4096) == cudaSuccess && cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaEventCreate(&e0) == cudaSuccess && cudaEventCreate(&e1) == cudaSuccess;
+    size_t partial_bytes = 0;
+    float best_ms = 1e30f;
+    char line[64];
+    g_tune_report.clear();
+    for (int id : kTuneCandidates) {
+        const Variant* v = find_variant(id);
+        Plan pl;
+        if (!ok || !v || make_plan(v, prop.multiProcessorCount, 0, kTuneBodies, kTuneBodies / v->UJ, &pl) != NBODY_OK) continue;
+        if (pl.partial_bytes > partial_bytes) {
+            cudaFree(partial);
+            partial = nullptr;
+            if (cudaMalloc(&partial, pl.partial_bytes) != cudaSuccess) { ok = false; continue; }
+            partial_bytes = pl.partial_bytes;
+        }
+        ForceArgs a{};
+        a.X = X; a.V = V; a.A = A; a.n_targets = kTuneBodies; a.src = src;
+        a.ra_count = kTuneBodies / v->UJ;
+        a.partial = partial; a.counters = counters; a.maxseg = pl.maxseg;
+        a.eps2 = 0.002f; a.dt = 0.f;   // dt = 0: the zeroed state stays put, every launch does identical work
+        float ms = 1e30f;
+        for (int rep = 0; rep < 3; ++rep) {   // first launch also loads the kernel image
+            cudaEventRecord(e0, st);
+            if (launch_force(v, pl, a, st) != NBODY_OK) { ms = 1e30f; break; }
+            cudaEventRecord(e1, st);
+            float t = 0.f;
+            if (cudaEventSynchronize(e1) != cudaSuccess || cudaEventElapsedTime(&t, e0, e1) != cudaSuccess) { ms = 1e30f; break; }
+            if (rep > 0 && t < ms) ms = t;
+        }
+        snprintf(line, sizeof line, "%s%d:%.3fms", g_tune_report.empty() ? "" : " ", id, ms);
+        g_tune_report += line;
+        if (ms < best_ms) { best_ms = ms; best = id; }
+    }
+    cudaGetLastError();
+    cudaFree(X); cudaFree(V); cudaFree(A); cudaFree(src); cudaFree(partial); cudaFree(counters);
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    if (st) cudaStreamDestroy(st);
+    g_tuned[dev] = best;
+    return best;
+}
+
 }  // namespace
 
 // ---- context ---------------------------------------------------------------------------------------
@@ -264,6 +350,7 @@ struct nbody_ctx {
     float4* partial = nullptr;
     unsigned* counters = nullptr;
     double* energy_part = nullptr;
+    unsigned long long* clk = nullptr;          // {clock64, globaltimer} x {entry, exit} of CTA 0 of the last force kernel
     float4* stage = nullptr;                     // upload staging, float4[n]
     Plan plan_full, plan_local, plan_remote;
     cudaStream_t stream = nullptr;
@@ -299,6 +386,7 @@ ForceArgs base_args(nbody_ctx* c)
     a.dt = c->p.dt;
     a.integ_f64 = c->p.integrator;   // 0 float, 1 double (headless flavour), 2 mixed (reduction flavours)
     a.dt64 = c->p.dt_f64;
+    a.clk = c->clk;
     return a;
 }
 
@@ -339,10 +427,18 @@ int nbody_variant_info(int id, char* buf, size_t buflen)
         if (v->small) snprintf(cl, sizeof cl, ", small-N family: %d targets/CTA, sources split over the CTA, warp-shuffle reduction", v->T);
         snprintf(buf, buflen, "%s: %d targets/thread, %d threads/CTA, %d sources/tile, unroll %d pairs, %s FP32, min %d CTAs/SM, %zu B smem%s",
                  v->name, v->T, v->NT, v->UJ, v->unroll,
-                 v->packed == 0 ? "scalar" : v->packed == 1 ? "packed f32x2" : v->packed == 2 ? "packed f32x2 (all FFMA2)" : v->packed == 3 ? "packed f32x2 + prefetch" : "packed f32x2 + first-pair prefetch",
+                 v->packed == 0 ? "scalar" : v->packed == 1 ? "packed f32x2" : v->packed == 2 ? "packed f32x2 (all FFMA2)" : v->packed == 3 ? "packed f32x2 + prefetch" : v->packed == 4 ? "packed f32x2 + first-pair prefetch" : v->packed == 5 ? "packed f32x2, targets reversed" : "packed f32x2, target-outer order",
                  v->minb, v->smem(), cl);
     }
     return kNumVariants;
+}
+
+int nbody_autotune_report(char* buf, size_t buflen)
+{
+    if (!buf || !buflen) return fail(NBODY_E_INVALID, "null buffer");
+    std::lock_guard<std::mutex> lk(g_tune_mu);
+    snprintf(buf, buflen, "%s", g_tune_report.c_str());
+    return NBODY_OK;
 }
 
 int nbody_variant_id(int index)
@@ -365,7 +461,7 @@ void nbody_destroy(nbody_ctx* c)
     if (c->step_graph) cudaGraphExecDestroy(c->step_graph);
     cudaFree(c->X); cudaFree(c->V); cudaFree(c->A); cudaFree(c->accum);
     cudaFree(c->packed[0]); cudaFree(c->packed[1]);
-    cudaFree(c->partial); cudaFree(c->counters); cudaFree(c->energy_part); cudaFree(c->stage); cudaFree(c->frame); cudaFree(c->frame_keys);
+    cudaFree(c->partial); cudaFree(c->counters); cudaFree(c->energy_part); cudaFree(c->clk); cudaFree(c->stage); cudaFree(c->frame); cudaFree(c->frame_keys);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -431,6 +527,8 @@ int nbody_create(nbody_ctx** out, const nbody_params* p)
     TRYCU(cudaMalloc(&c->packed[0], sb));
     TRYCU(cudaMalloc(&c->packed[1], sb));
     TRYCU(cudaMalloc(&c->partial, partial_bytes));
+    TRYCU(cudaMalloc(&c->clk, 4 * sizeof(unsigned long long)));
+    TRYCU(cudaMemset(c->clk, 0, 4 * sizeof(unsigned long long)));
     TRYCU(cudaMalloc(&c->counters, (size_t)c->plan_full.num_counters * sizeof(unsigned)));
     TRYCU(cudaMemset(c->V, 0, tb));
     TRYCU(cudaMemset(c->A, 0, tb));

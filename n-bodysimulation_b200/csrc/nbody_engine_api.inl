@@ -153,6 +153,19 @@ int nbody_elapsed_ms(nbody_ctx* c, float* ms)
     return NBODY_OK;
 }
 
+int nbody_kernel_clock_mhz(nbody_ctx* c, float* mhz)
+{
+    if (!c || !mhz) return fail(NBODY_E_INVALID, "null argument");
+    int rc = set_device(c);
+    if (rc) return rc;
+    unsigned long long h[4];
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaMemcpy(h, c->clk, sizeof h, cudaMemcpyDeviceToHost));
+    if (h[3] <= h[1] || h[2] <= h[0]) return fail(NBODY_E_STATE, "no stream-K force kernel has run on this context yet");
+    *mhz = (float)((double)(h[2] - h[0]) / (double)(h[3] - h[1]) * 1e3);   // cycles per ns -> MHz
+    return NBODY_OK;
+}
+
 int nbody_energy(nbody_ctx* c, double* ke, double* pe)
 {
     if (!c || !ke || !pe) return fail(NBODY_E_INVALID, "null argument");

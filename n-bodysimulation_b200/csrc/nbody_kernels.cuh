@@ -56,6 +56,8 @@ struct ForceArgs {
     int va_f3;            // 1: V and A are packed float3 arrays (FLOAT_3 build of the reference, main.cpp:233-269)
     double dt64;
     float k_one, k_negzero;   // 1.0f and -0.0f as run-time values (MODE 2 keeps ptxas from folding x*1+y)
+    // optional: CTA 0 records {clock64, globaltimer} at entry and exit -> SM clock actually run at
+    unsigned long long* clk;
 };
 
 // ---- integrator + stores for one target (TestProject/kernel.cu:116-129) -------------
@@ -146,7 +148,8 @@ __device__ __forceinline__ int unit_owner(u64 u, u64 U, u64 W) { return (int)(((
 
 // MODE: 0 scalar FFMA | 1 packed FADD2/FMUL2/FFMA2 | 2 packed, every op issued as FFMA2
 //       (x*1+y, x*y-0: bit-identical results) | 3 packed + source pairs prefetched one group ahead
-//       | 4 packed + only the next group's FIRST pair prefetched
+//       | 4 packed + only the next group's FIRST pair prefetched | 5, 6 packed, same arithmetic in another
+//       source order (targets reversed / target-outer): ptxas' register allocation differs by a few per cent
 // CS / CMODE: thread-block clusters (launch attribute clusterDim = CS).
 //   CMODE 1 "multicast": the CS CTAs of a cluster own CS neighbouring target tiles and stream
 //           the SAME source units; CTA r fetches slice r of each unit and TMA-multicasts it
@@ -177,6 +180,7 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
     float4* s_red = reinterpret_cast<float4*>(smem_raw + kStages * kStageBytes + 16 * kStages + 16);   // JSPLIT only: [TI]
 
     const int tid = threadIdx.x, lane = tid & 31;
+    if (a.clk && blockIdx.x == 0 && tid == 0) { a.clk[0] = clock64(); a.clk[1] = globaltimer_ns(); }
     const uint32_t crank = CS > 1 ? cluster_ctarank() : 0u;
     const int J = a.ra_count + a.rb_count;
     const int num_itiles = (a.n_targets + TS - 1) / TS;
@@ -198,7 +202,11 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
     // ---- producer state (thread 0 only) ------------------------------------------------
     // JSPLIT: within each segment (part of one tile's unit row inside [u_begin, u_end)) this
     // CTA takes the units at offset crank, crank+CS, ... from the segment start.
-    u64 pu = u_begin;                   // next linear unit to consider
+    // Producer bookkeeping is 32-bit and division-free outside JSPLIT: it runs in warp 0 once per
+    // unit, and a 64-bit modulo there cost 3 % of the whole kernel (r1: 2 730 -> 2 630 G/s).
+    u64 pu = u_begin;                   // next linear unit to consider (JSPLIT walks it unit by unit)
+    int pj = (int)(u_begin % (u64)J);   // its source unit, index into A|B
+    int pleft = (int)(u_end - u_begin); // units still to fetch (non-JSPLIT)
     int kf = 0;                         // fetches issued so far
     auto issue = [&]() -> bool {
         if (JSPLIT) {
@@ -208,9 +216,13 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
                 if ((pu - seg0) % CS == crank) break;
                 ++pu;
             }
+            if (pu >= u_end) return false;
+            pj = (int)(pu % (u64)J);
+            ++pu;
+        } else {
+            if (pleft <= 0) return false;
+            --pleft;
         }
-        if (pu >= u_end) return false;
-        const int pj = (int)(pu % (u64)J);
         const int s = kf & (kStages - 1), n = kf / kStages;
         if (n > 0) mbar_wait(bar_empty + 8 * s, (n - 1) & 1);
         const int ju = pj < a.ra_count ? a.ra_begin + pj : a.rb_begin + (pj - a.ra_count);
@@ -222,7 +234,7 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
         } else {
             tma_bulk_g2s(smem_base + s * kStageBytes, a.src + (size_t)ju * UJ, kStageBytes, bar_full + 8 * s);
         }
-        ++pu;
+        if (!JSPLIT && ++pj == J) pj = 0;
         ++kf;
         return true;
     };
@@ -268,7 +280,8 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
             // two interactions (one source pair) against every target held by this thread
             auto interact2 = [&](const ulonglong2 xy, const ulonglong2 zm) {
 #pragma unroll
-                for (int t = 0; t < T; ++t) {
+                for (int tt = 0; tt < T; ++tt) {
+                    const int t = MODE == 5 ? T - 1 - tt : tt;   // MODE 5: same arithmetic, targets visited in reverse
                     const u64 dx = ADD2(xy.x, nx[t]);
                     const u64 dy = ADD2(xy.y, ny[t]);
                     const u64 dz = ADD2(zm.x, nz[t]);
@@ -284,7 +297,32 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
                     az[t] = fma2(dz, sc, az[t]);
                 }
             };
-            if (MODE == 3) {
+            if (MODE == 6) {
+                // MODE 6: same arithmetic, target-outer / pair-inner order inside a group of UNROLL pairs
+#pragma unroll 1
+                for (int p = 0; p < UJ / 2; p += UNROLL) {
+                    ulonglong2 gxy[UNROLL], gzm[UNROLL];
+#pragma unroll
+                    for (int q = 0; q < UNROLL; ++q) { gxy[q] = sp[2 * (p + q)]; gzm[q] = sp[2 * (p + q) + 1]; }
+#pragma unroll
+                    for (int t = 0; t < T; ++t) {
+#pragma unroll
+                        for (int q = 0; q < UNROLL; ++q) {
+                            const u64 dx = add2(gxy[q].x, nx[t]), dy = add2(gxy[q].y, ny[t]), dz = add2(gzm[q].x, nz[t]);
+                            u64 r2 = fma2(dx, dx, eps2p);
+                            r2 = fma2(dy, dy, r2);
+                            r2 = fma2(dz, dz, r2);
+                            const u64 d3 = mul2(mul2(r2, r2), r2);
+                            float lo, hi;
+                            unpack2(d3, lo, hi);
+                            const u64 sc = mul2(pack2(rsqrt_mufu(lo), rsqrt_mufu(hi)), gzm[q].y);
+                            ax[t] = fma2(dx, sc, ax[t]);
+                            ay[t] = fma2(dy, sc, ay[t]);
+                            az[t] = fma2(dz, sc, az[t]);
+                        }
+                    }
+                }
+            } else if (MODE == 3) {
                 ulonglong2 cxy[UNROLL], czm[UNROLL];
 #pragma unroll
                 for (int q = 0; q < UNROLL; ++q) { cxy[q] = sp[2 * q]; czm[q] = sp[2 * q + 1]; }
@@ -473,6 +511,7 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
         }
         u += (u64)jn;
     }
+    if (a.clk && blockIdx.x == 0 && tid == 0) { a.clk[2] = clock64(); a.clk[3] = globaltimer_ns(); }
     if (CS > 1) cluster_sync_all();   // no CTA leaves while peers may still touch its shared memory
 }
 

@@ -48,6 +48,13 @@ __device__ __forceinline__ float rsqrt_mufu(float x)
     return y;
 }
 
+__device__ __forceinline__ unsigned long long globaltimer_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 // ---- shared memory ------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p)
 {
