@@ -132,6 +132,15 @@ const Variant kVariants[] = {
     VARIANT(94, 7, 256, 256, 2, 6, 1),
     VARIANT(95, 6, 256, 256, 4, 6, 1),
     VARIANT(96, 8, 256, 512, 2, 6, 1),
+    VARIANT(97, 6, 256, 256, 2, 7, 1),
+    VARIANT(98, 6, 256, 256, 2, 8, 1),
+    VARIANT(99, 8, 256, 256, 2, 7, 1),
+    VARIANT(100, 8, 256, 512, 2, 8, 1),
+    VARIANT(101, 6, 256, 512, 2, 5, 1),
+    VARIANT(102, 6, 256, 512, 2, 7, 1),
+    VARIANT(103, 6, 256, 1024, 2, 5, 1),
+    VARIANT(104, 6, 256, 1024, 2, 1, 1),
+    VARIANT(105, 6, 256, 512, 2, 1, 1),
     // thread-block-cluster variants: m1 = TMA multicast, m2 = j-split with DSMEM reduction
     CVARIANT(60, 6, 256, 256, 2, 1, 1, 2, 1),
     CVARIANT(61, 6, 256, 256, 2, 1, 1, 4, 1),
@@ -265,7 +274,7 @@ int launch_pack(const float4* X, int n, float4* packed, int off, int n_cover, cu
 // worth +-3.5 % (register-bank conflicts on the 3-operand FFMA2; profiles/r1_variant_sweep_*).  Rather
 // than trust one allocation, the first large context of a process times each candidate for ~1 ms on
 // synthetic bodies and keeps the fastest (NBODY_LARGE_VARIANT=<id> in the environment overrides).
-const int kTuneCandidates[] = {45, 90, 91, 21, 92, 93, 96};
+const int kTuneCandidates[] = {45, 90, 96, 97, 98, 101, 102, 105};   // UJ 1024 (103, 104) is 0.3 % faster at N = 1 M but 4 % slower at the tuner's size: opt-in
 constexpr int kTuneBodies = 49152;   // whole tiles for T6 (1536) and T8 (2048): 0.9 ms per launch
 std::mutex g_tune_mu;
 std::map<int, int> g_tuned;          // device -> variant id
@@ -427,7 +436,7 @@ int nbody_variant_info(int id, char* buf, size_t buflen)
         if (v->small) snprintf(cl, sizeof cl, ", small-N family: %d targets/CTA, sources split over the CTA, warp-shuffle reduction", v->T);
         snprintf(buf, buflen, "%s: %d targets/thread, %d threads/CTA, %d sources/tile, unroll %d pairs, %s FP32, min %d CTAs/SM, %zu B smem%s",
                  v->name, v->T, v->NT, v->UJ, v->unroll,
-                 v->packed == 0 ? "scalar" : v->packed == 1 ? "packed f32x2" : v->packed == 2 ? "packed f32x2 (all FFMA2)" : v->packed == 3 ? "packed f32x2 + prefetch" : v->packed == 4 ? "packed f32x2 + first-pair prefetch" : v->packed == 5 ? "packed f32x2, targets reversed" : "packed f32x2, target-outer order",
+                 v->packed == 0 ? "scalar" : v->packed == 1 ? "packed f32x2" : v->packed == 2 ? "packed f32x2 (all FFMA2)" : v->packed == 3 ? "packed f32x2 + prefetch" : v->packed == 4 ? "packed f32x2 + first-pair prefetch" : v->packed == 5 ? "packed f32x2, targets reversed" : v->packed == 6 ? "packed f32x2, target-outer order" : "packed f32x2, z-first order",
                  v->minb, v->smem(), cl);
     }
     return kNumVariants;

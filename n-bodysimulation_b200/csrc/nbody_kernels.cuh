@@ -281,10 +281,10 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
             auto interact2 = [&](const ulonglong2 xy, const ulonglong2 zm) {
 #pragma unroll
                 for (int tt = 0; tt < T; ++tt) {
-                    const int t = MODE == 5 ? T - 1 - tt : tt;   // MODE 5: same arithmetic, targets visited in reverse
-                    const u64 dx = ADD2(xy.x, nx[t]);
-                    const u64 dy = ADD2(xy.y, ny[t]);
-                    const u64 dz = ADD2(zm.x, nz[t]);
+                    const int t = (MODE == 5 || MODE == 8) ? T - 1 - tt : tt;   // MODE 5/8: same arithmetic, targets visited in reverse
+                    u64 dx, dy, dz;
+                    if (MODE == 7 || MODE == 8) { dz = ADD2(zm.x, nz[t]); dy = ADD2(xy.y, ny[t]); dx = ADD2(xy.x, nx[t]); }   // z first
+                    else { dx = ADD2(xy.x, nx[t]); dy = ADD2(xy.y, ny[t]); dz = ADD2(zm.x, nz[t]); }
                     u64 r2 = fma2(dx, dx, eps2p);
                     r2 = fma2(dy, dy, r2);
                     r2 = fma2(dz, dz, r2);
@@ -292,9 +292,8 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
                     float lo, hi;
                     unpack2(d3, lo, hi);
                     const u64 sc = MUL2(pack2(rsqrt_mufu(lo), rsqrt_mufu(hi)), zm.y);
-                    ax[t] = fma2(dx, sc, ax[t]);
-                    ay[t] = fma2(dy, sc, ay[t]);
-                    az[t] = fma2(dz, sc, az[t]);
+                    if (MODE == 7 || MODE == 8) { az[t] = fma2(dz, sc, az[t]); ay[t] = fma2(dy, sc, ay[t]); ax[t] = fma2(dx, sc, ax[t]); }
+                    else { ax[t] = fma2(dx, sc, ax[t]); ay[t] = fma2(dy, sc, ay[t]); az[t] = fma2(dz, sc, az[t]); }
                 }
             };
             if (MODE == 6) {
