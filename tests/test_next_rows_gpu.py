@@ -232,3 +232,14 @@ def test_graph_replayed_steps_equal_single_steps(cuda, nb, n):
         replayed = sim.download()
     for a, b in zip(one_by_one, replayed):
         assert np.array_equal(a, b)
+
+
+def test_large_contexts_pick_their_kernel_by_measurement(cuda, nb):
+    with nb.Simulation(16384) as sim:                          # >= 12288 bodies: resolved through the tuner
+        name = sim.info()["variant_name"]
+    rep = nb.autotune_report()
+    assert name.startswith(("T6_NT256", "T8_NT256"))
+    cands = dict(item.split(":") for item in rep.split())
+    assert len(cands) >= 4 and all(0.1 < float(ms[:-2]) < 50 for ms in cands.values()), rep
+    best = min(cands, key=lambda k: float(cands[k][:-2]))
+    assert nb.variants()[int(best)].split(":")[0] == name
