@@ -172,7 +172,7 @@ const Variant* find_variant(int id)
     return nullptr;
 }
 
-int tuned_large_variant();
+int tuned_large_variant(int n_sources);
 
 int auto_variant(int n_targets, int n_sources)
 {
@@ -182,7 +182,7 @@ int auto_variant(int n_targets, int n_sources)
         if (n_sources < 3072) return 85; // 2 targets / CTA, sources split over 128 threads, shuffle reduction
         return 82;                       // 4 targets / CTA
     }
-    if (n_targets >= 12288) return tuned_large_variant();   // T6/T8 x 256 threads, 1 CTA/SM: picked by measurement
+    if (n_targets >= 12288) return tuned_large_variant(n_sources);   // T6/T8 x 256 threads, 1 CTA/SM: picked by measurement
     if (n_targets >= 2048) return 3;     // T2 x 256 threads, 3 CTAs/SM
     return 12;                           // T1 x 128 threads, 64-body units
 }
@@ -277,20 +277,22 @@ int launch_pack(const float4* X, int n, float4* packed, int off, int n_cover, cu
 const int kTuneCandidates[] = {45, 90, 96, 97, 98, 101, 102, 105};   // UJ 1024 (103, 104) is 0.3 % faster at N = 1 M but 4 % slower at the tuner's size: opt-in
 constexpr int kTuneBodies = 49152;   // whole tiles for T6 (1536) and T8 (2048): 0.9 ms per launch
 std::mutex g_tune_mu;
-std::map<int, int> g_tuned;          // device -> variant id
+std::map<int, std::pair<int, int>> g_tuned;   // device -> (best with 256-body units, best overall)
 std::string g_tune_report;
 
-int tuned_large_variant()
+int tuned_large_variant(int n_sources)
 {
+    // 512-body units win at N >= 64 k (fewer barrier round trips) but cut a 16 k-body step into too few pieces
+    const bool small_units = n_sources < 65536;
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return 45;
     std::lock_guard<std::mutex> lk(g_tune_mu);
     auto it = g_tuned.find(dev);
-    if (it != g_tuned.end()) return it->second;
-    int best = 45;
+    if (it != g_tuned.end()) return small_units ? it->second.first : it->second.second;
+    int best = 45, best256 = 45;
     if (const char* env = getenv("NBODY_LARGE_VARIANT")) {
         const int id = atoi(env);
-        if (find_variant(id) && !find_variant(id)->small) { g_tuned[dev] = id; g_tune_report = "forced by NBODY_LARGE_VARIANT"; return id; }
+        if (find_variant(id) && !find_variant(id)->small) { g_tuned[dev] = std::make_pair(id, id); g_tune_report = "forced by NBODY_LARGE_VARIANT"; return id; }
     }
     cudaDeviceProp prop;
     float4 *X = nullptr, *V = nullptr, *A = nullptr, *src = nullptr, *partial = nullptr;
@@ -304,7 +306,7 @@ int tuned_large_variant()
               cudaMemset(counters, 0, 4096) == cudaSuccess && cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) == cudaSuccess &&
               cudaEventCreate(&e0) == cudaSuccess && cudaEventCreate(&e1) == cudaSuccess;
     size_t partial_bytes = 0;
-    float best_ms = 1e30f;
+    float best_ms = 1e30f, best256_ms = 1e30f;
     char line[64];
     g_tune_report.clear();
     for (int id : kTuneCandidates) {
@@ -334,14 +336,15 @@ int tuned_large_variant()
         snprintf(line, sizeof line, "%s%d:%.3fms", g_tune_report.empty() ? "" : " ", id, ms);
         g_tune_report += line;
         if (ms < best_ms) { best_ms = ms; best = id; }
+        if (v->UJ == 256 && ms < best256_ms) { best256_ms = ms; best256 = id; }
     }
     cudaGetLastError();
     cudaFree(X); cudaFree(V); cudaFree(A); cudaFree(src); cudaFree(partial); cudaFree(counters);
     if (e0) cudaEventDestroy(e0);
     if (e1) cudaEventDestroy(e1);
     if (st) cudaStreamDestroy(st);
-    g_tuned[dev] = best;
-    return best;
+    g_tuned[dev] = std::make_pair(best256, best);
+    return small_units ? best256 : best;
 }
 
 }  // namespace

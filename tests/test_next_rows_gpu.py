@@ -241,5 +241,9 @@ def test_large_contexts_pick_their_kernel_by_measurement(cuda, nb):
     assert name.startswith(("T6_NT256", "T8_NT256"))
     cands = dict(item.split(":") for item in rep.split())
     assert len(cands) >= 4 and all(0.1 < float(ms[:-2]) < 50 for ms in cands.values()), rep
-    best = min(cands, key=lambda k: float(cands[k][:-2]))
+    small_units = [k for k in cands if "_UJ256_" in nb.variants()[int(k)]]      # 16 k bodies: 256-body units only
+    best = min(small_units, key=lambda k: float(cands[k][:-2]))
     assert nb.variants()[int(best)].split(":")[0] == name
+    with nb.Simulation(70000) as sim:                          # >= 64 k sources: best of all candidates
+        best_all = min(cands, key=lambda k: float(cands[k][:-2]))
+        assert sim.info()["variant_name"] == nb.variants()[int(best_all)].split(":")[0]

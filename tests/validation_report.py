@@ -1,0 +1,114 @@
+"""validation_report.py -- run record of a whole validation pass, by hand on a B200:
+
+    python tests/validation_report.py [out.json]
+
+For each BASELINE.json config that fits one GPU it steps the engine in lock-step with the checker's snapshot
+reading of the reference's CPU path (oracle O2; the reference's compareHostToDevice idea, validation.cpp:55-103,
+with a checker that is consistent with a GPU kernel) and records per-step errors, the reference's own 1 % test
+(verify_still_bodies), energy drift and device-timed throughput.  Lives under tests/ because it uses oracle/."""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "oracle")):
+    sys.path.insert(0, p)
+import nbody_b200 as nb  # noqa: E402
+import oracle as o       # noqa: E402
+
+
+def rate(n, ms):
+    return round(n * float(n) / ms / 1e6, 1)
+
+
+def lockstep(n, steps, x0, v0=None, dt=0.1):
+    """engine and O2 advanced side by side; error of the engine's state against O2's after every step"""
+    X, V, A = x0.copy(), (np.zeros_like(x0) if v0 is None else v0.copy()), np.zeros_like(x0)
+    rows, ms_total = [], 0.0
+    with nb.Simulation(n, dt=dt) as sim:
+        sim.upload(x0, v0)
+        name = sim.info()["variant_name"]
+        for s in range(steps):
+            sim.step(1)
+            ms_total += sim.elapsed_ms()
+            o.step_snapshot(X, A, V, dt=dt)
+            x, v, a = sim.download()
+            rows.append({"step": s + 1, "err_a": o.norm_rel_err(a, A), "err_x": o.norm_rel_err(x, X), "err_v": o.norm_rel_err(v, V),
+                         "reference_1pct_test_failures_x": int(o.verify_still_bodies(x, X))})
+    return name, rows, ms_total / steps
+
+
+def main():
+    out = {"when": time.strftime("%Y-%m-%dT%H:%M:%SZ", time.gmtime()), "configs": []}
+
+    # config 1: N = 1024, reference ICs (fill_with_random4), 10 steps
+    n = 1024
+    name, rows, ms = lockstep(n, 10, o.ic_reference(n))
+    out["configs"].append({"config": 1, "n": n, "ic": "reference fill_with_random4", "kernel": name, "steps": rows,
+                           "ms_per_step_single_launches": round(ms, 5), "g_inter_per_s": rate(n, ms),
+                           "ok": bool(rows[0]["err_a"] <= 1e-5 and rows[-1]["err_x"] <= 1e-5 and rows[-1]["reference_1pct_test_failures_x"] == 0)})
+
+    # config 2: N = 16384, checked per step
+    n = 16384
+    x0 = nb.ic_uniform(n, seed=12345)
+    name, rows, ms = lockstep(n, 10, x0)
+    a64 = o.accel_f64(x0)
+    Xr, Vr, Ar = x0.copy(), np.zeros_like(x0), np.zeros_like(x0)
+    o.step_snapshot(Xr, Ar, Vr)
+    with nb.Simulation(n) as sim:
+        sim.upload(x0).step(1)
+        _, _, a1 = sim.download()
+    e_ours, e_ref = o.norm_rel_err(a1, a64), o.norm_rel_err(Ar, a64)
+    out["configs"].append({"config": 2, "n": n, "ic": "uniform seed 12345", "kernel": name, "steps": rows,
+                           "err_a_vs_fp64_step1": e_ours, "reference_fp32_err_vs_fp64_step1": e_ref,
+                           "ms_per_step_single_launches": round(ms, 4), "g_inter_per_s": rate(n, ms),
+                           "ok": bool(e_ours <= max(1e-5, 1.5 * e_ref))})
+
+    # config 3: N = 131072 Plummer, 100 steps, effective-energy drift (E_eff = KE + PE/2)
+    n = 131072
+    x0, v0 = nb.ic_plummer(n, seed=12345)
+    with nb.Simulation(n, dt=0.01) as sim:
+        sim.upload(x0, v0)
+        ke0, pe0 = sim.energy()
+        sim.step(100)
+        ms = sim.elapsed_ms() / 100
+        ke1, pe1 = sim.energy()
+        name = sim.info()["variant_name"]
+    e0, e1 = ke0 + 0.5 * pe0, ke1 + 0.5 * pe1
+    out["configs"].append({"config": 3, "n": n, "ic": "Plummer seed 12345, dt 0.01", "kernel": name, "steps_run": 100,
+                           "e_eff_0": e0, "e_eff_100": e1, "drift_rel": abs(e1 - e0) / abs(e0), "virial_2ke_over_half_pe": 2 * ke0 / (-0.5 * pe0),
+                           "ms_per_step": round(ms, 4), "g_inter_per_s": rate(n, ms), "ok": bool(abs(e1 - e0) / abs(e0) <= 1e-3)})
+
+    # config 4 (one GPU): N = 1 048 576, sampled targets vs fp64, momentum balance
+    n = 1 << 20
+    x0 = nb.ic_uniform(n, seed=12345)
+    with nb.Simulation(n) as sim:
+        sim.upload(x0).step(1)
+        sim.step(3)
+        ms = sim.elapsed_ms() / 3
+        name = sim.info()["variant_name"]
+    with nb.Simulation(n) as sim:
+        sim.upload(x0).step(1)
+        _, _, a = sim.download()
+    idx = np.random.default_rng(1).choice(n, 128, replace=False).astype(np.int32)
+    a64 = o.accel_f64(x0, idx)
+    e_ours, e_ref = o.norm_rel_err(a[idx], a64), o.norm_rel_err(o.accel_f32(x0, idx), a64)
+    f = a[:, :3].astype(np.float64) * x0[:, 3:4].astype(np.float64)
+    out["configs"].append({"config": 4, "n": n, "ic": "uniform seed 12345", "kernel": name, "sampled_targets": 128,
+                           "err_a_vs_fp64": e_ours, "reference_fp32_err_vs_fp64": e_ref,
+                           "momentum_residual_rel": float(np.linalg.norm(f.sum(0)) / np.abs(f).sum()),
+                           "ms_per_step": round(ms, 3), "g_inter_per_s": rate(n, ms), "pct_fp32_peak_1965": round(100 * rate(n, ms) * 20e9 / (148 * 128 * 2 * 1.965e9), 2),
+                           "autotune": nb.autotune_report(), "ok": bool(e_ours <= max(1e-5, 2 * e_ref))})
+    out["ok"] = all(c["ok"] for c in out["configs"])
+    text = json.dumps(out, indent=1)
+    if len(sys.argv) > 1:
+        open(sys.argv[1], "w").write(text + "\n")
+    print(json.dumps({"ok": out["ok"], "configs": [{k: c[k] for k in ("config", "n", "kernel", "g_inter_per_s", "ok")} for c in out["configs"]]}))
+    return 0 if out["ok"] else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())
