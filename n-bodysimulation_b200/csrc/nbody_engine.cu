@@ -141,6 +141,13 @@ const Variant kVariants[] = {
     VARIANT(103, 6, 256, 1024, 2, 5, 1),
     VARIANT(104, 6, 256, 1024, 2, 1, 1),
     VARIANT(105, 6, 256, 512, 2, 1, 1),
+    // finer source units for mid-size N (cost model in mid_variant): same kernels, 64- / 128-body units
+    VARIANT(110, 8, 256, 128, 2, 6, 1),
+    VARIANT(111, 8, 256, 64, 2, 6, 1),
+    VARIANT(112, 6, 256, 128, 2, 5, 1),
+    VARIANT(113, 6, 256, 64, 2, 5, 1),
+    VARIANT(114, 4, 256, 128, 4, 1, 2),
+    VARIANT(115, 8, 256, 128, 2, 1, 1),
     // thread-block-cluster variants: m1 = TMA multicast, m2 = j-split with DSMEM reduction
     CVARIANT(60, 6, 256, 256, 2, 1, 1, 2, 1),
     CVARIANT(61, 6, 256, 256, 2, 1, 1, 4, 1),
@@ -173,6 +180,8 @@ const Variant* find_variant(int id)
 }
 
 int tuned_large_variant(int n_sources);
+int mid_variant(int n_targets, int n_sources);
+constexpr int kSlotAlignBodies = 1024;   // = kSlotAlign below
 
 int auto_variant(int n_targets, int n_sources)
 {
@@ -182,9 +191,34 @@ int auto_variant(int n_targets, int n_sources)
         if (n_sources < 3072) return 85; // 2 targets / CTA, sources split over 128 threads, shuffle reduction
         return 82;                       // 4 targets / CTA
     }
-    if (n_targets >= 12288) return tuned_large_variant(n_sources);   // T6/T8 x 256 threads, 1 CTA/SM: picked by measurement
+    if (n_targets >= 12288 && n_sources < 65536) return mid_variant(n_targets, n_sources);
+    if (n_targets >= 12288) return tuned_large_variant(n_sources);
     if (n_targets >= 2048) return 3;     // T2 x 256 threads, 3 CTAs/SM
     return 12;                           // T1 x 128 threads, 64-body units
+}
+
+// Mid-size N (12 k ... 64 k bodies, a step of 0.1 - 1.5 ms): the kernel's time is (units of the busiest CTA) x
+// (time per unit), and with only a few units per CTA the rounding of units / CTAs and the padding of the last
+// target tile are worth several per cent (N = 16 384, T6 x 256-body units: 704 units on 148 CTAs -> 5 where 4.76
+// are needed, and the 11th tile is 2/3 empty).  Pick the tile shape and unit size that minimise that product.
+int mid_variant(int n_targets, int n_sources)
+{
+    struct Cand { int id, T, UJ; };
+    static const Cand cands[] = {{90, 6, 256}, {112, 6, 128}, {113, 6, 64}, {93, 8, 256}, {110, 8, 128}, {111, 8, 64}};
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const long long src_pad = (long long)(n_sources + kSlotAlignBodies - 1) / kSlotAlignBodies * kSlotAlignBodies;
+    double best_cost = 1e300;
+    int best = 90;
+    for (const Cand& c : cands) {
+        const long long tiles = (n_targets + c.T * 256 - 1) / (c.T * 256), J = src_pad / c.UJ, U = tiles * J;
+        const long long maxu = (U + sms - 1) / sms;
+        // cycles per unit: UJ/4 loop iterations of (T x 24 packed ops x 2 + ~35) cycles, plus ~150 of barrier / producer work
+        // (the T8 kernels measure ~2.5 % slower per interaction than T6 at equal balance: 250 vs 192 registers)
+        const double cost = (double)maxu * ((c.UJ / 4) * (c.T * 48.0 + 35.0) + 150.0) * (c.T == 8 ? 1.025 : 1.0);
+        if (cost < best_cost) { best_cost = cost; best = c.id; }
+    }
+    return best;
 }
 
 int round_up(int v, int m) { return (v + m - 1) / m * m; }
