@@ -281,6 +281,16 @@ int nbody_shard_attach_ptr(nbody_ctx* c, int peer, void* buf0, void* buf1)
     int rc = attach_checks(c, peer);
     if (rc) return rc;
     if (!buf0 || !buf1) return fail(NBODY_E_INVALID, "null buffer");
+    // same process, other device: the stores need peer access from this context's device
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, buf0) == cudaSuccess && at.type == cudaMemoryTypeDevice && at.device != c->p.device) {
+        int can = 0;
+        CU(cudaDeviceCanAccessPeer(&can, c->p.device, at.device));
+        if (!can) return fail(NBODY_E_CUDA, "device %d cannot access device %d (no P2P path)", c->p.device, at.device);
+        const cudaError_t e = cudaDeviceEnablePeerAccess(at.device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(NBODY_E_CUDA, "cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
+        cudaGetLastError();
+    }
     c->peer_packed[peer][0] = (float4*)buf0; c->peer_packed[peer][1] = (float4*)buf1;
     ++c->peers_attached;
     return NBODY_OK;

@@ -13,12 +13,15 @@
 //                  [--flavour simulate|emb|emb-float3]   which launcher of kernel.cuh:2-7 (headless forms)
 //                  [--ppm FILE]                          final frame (the reference's GL draw as CUDA)
 //                  [--save FILE] [--load FILE]           snapshot / resume (with --resident)
+//                  [--gpus G]                            G GPUs of this box from ONE process: each owns N/G targets,
+//                                                        fused P2P exchange, cross-device events as the barrier
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <exception>
 #include <iostream>
 #include <string>
+#include <vector>
 
 #include "../../include/kernel.cuh"
 #include "../../include/nbody_b200.h"
@@ -72,6 +75,7 @@ int main(int argc, char** argv)
     float eps2 = EPS2, dt = DT;
     std::string ic = "reference", flavour = "simulate", ppm, save, load;
     bool resident = false, host_f3 = false, json = false;
+    int gpus = 1;
     for (int i = 1; i < argc; ++i) {
         auto need = [&](const char* f) { if (i + 1 >= argc) { fprintf(stderr, "%s needs a value\n", f); exit(2); } return argv[++i]; };
         if (!strcmp(argv[i], "--n")) n = atoi(need("--n"));
@@ -83,6 +87,7 @@ int main(int argc, char** argv)
         else if (!strcmp(argv[i], "--resident")) resident = true;
         else if (!strcmp(argv[i], "--host-f3")) host_f3 = true;
         else if (!strcmp(argv[i], "--json")) json = true;
+        else if (!strcmp(argv[i], "--gpus")) gpus = atoi(need("--gpus"));
         else if (!strcmp(argv[i], "--flavour")) flavour = need("--flavour");
         else if (!strcmp(argv[i], "--ppm")) ppm = need("--ppm");
         else if (!strcmp(argv[i], "--save")) save = need("--save");
@@ -109,7 +114,60 @@ int main(int argc, char** argv)
 
     int rc = 0;
     float ms = -1.f, ms_first = -1.f, ms_steady = -1.f;
-    if (host_f3) {
+    if (gpus > 1) {
+        // One process, G contexts (rank g on device g).  The reference is single-GPU (kernel.cu:630 asks for device 0);
+        // this is the C++ face of the fused exchange: every step is ONE kernel per GPU whose epilogue stores the new
+        // positions into every GPU's next source buffer, and "all GPUs have finished step s" is expressed with events
+        // (each stream waits for every other GPU's event) -- no collective library, no host synchronisation in the loop.
+        std::vector<nbody_ctx*> ctx(gpus, nullptr);
+        std::vector<cudaStream_t> st(gpus);
+        std::vector<cudaEvent_t> ev(gpus);
+        bool ok = true;
+        for (int g = 0; g < gpus && ok; ++g) {
+            nbody_params p;
+            nbody_params_default(&p);
+            p.n_bodies = n; p.eps2 = eps2; p.dt = dt; p.rank = g; p.world = gpus; p.device = g;
+            ok = nbody_create(&ctx[g], &p) == NBODY_OK && nbody_upload(ctx[g], (float*)bodies, (float*)velocity) == NBODY_OK &&
+                 cudaSetDevice(g) == cudaSuccess && cudaStreamCreateWithFlags(&st[g], cudaStreamNonBlocking) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&ev[g], cudaEventDisableTiming) == cudaSuccess;
+        }
+        for (int g = 0; g < gpus && ok; ++g)
+            for (int h = 0; h < gpus && ok; ++h) {
+                void *b0, *b1;
+                if (h != g) ok = nbody_shard_buffers(ctx[h], &b0, &b1) == NBODY_OK && nbody_shard_attach_ptr(ctx[g], h, b0, b1) == NBODY_OK;
+            }
+        if (!ok) { std::cerr << nbody_last_error() << std::endl; return EXIT_FAILURE; }
+        cudaEvent_t t0, t1;
+        cudaSetDevice(0);
+        cudaEventCreate(&t0); cudaEventCreate(&t1);
+        printf("Starting the simulation...\n");
+        cudaEventRecord(t0, st[0]);
+        for (int s = 0; s < steps && ok; ++s) {
+            for (int g = 0; g < gpus && ok; ++g) {
+                cudaSetDevice(g);
+                ok = nbody_shard_step_fused_async(ctx[g], st[g]) == NBODY_OK && cudaEventRecord(ev[g], st[g]) == cudaSuccess;
+            }
+            for (int g = 0; g < gpus && ok; ++g) {      // barrier: nobody starts step s+1 before everybody finished step s
+                cudaSetDevice(g);
+                for (int h = 0; h < gpus; ++h)
+                    if (h != g) ok = ok && cudaStreamWaitEvent(st[g], ev[h], 0) == cudaSuccess;
+            }
+        }
+        cudaSetDevice(0);
+        cudaEventRecord(t1, st[0]);
+        for (int g = 0; g < gpus; ++g) { cudaSetDevice(g); ok = ok && cudaStreamSynchronize(st[g]) == cudaSuccess; }
+        if (!ok) { std::cerr << "multi-GPU run failed: " << nbody_last_error() << " / " << cudaGetErrorString(cudaGetLastError()) << std::endl; rc = EXIT_FAILURE; }
+        else printf("Simulation complete\n");
+        cudaSetDevice(0);
+        cudaEventElapsedTime(&ms, t0, t1);
+        for (int g = 0; g < gpus; ++g) {
+            int b = 0, cnt = 0;
+            nbody_owned_range(ctx[g], &b, &cnt);
+            nbody_download(ctx[g], (float*)(bodies + b), (float*)(velocity + b), (float*)(accelerations + b));
+        }
+        for (int g = 0; g < gpus; ++g) { nbody_destroy(ctx[g]); cudaSetDevice(g); cudaStreamDestroy(st[g]); cudaEventDestroy(ev[g]); }
+        cudaSetDevice(0);
+    } else if (host_f3) {
         // headless-directory flavour: host pointers, float3 velocity (its constants: EPS2 0.002, DT 0.01)
         float3* v3 = new float3[n];
         float3* a3 = new float3[n];
@@ -196,7 +254,7 @@ int main(int argc, char** argv)
         printf("{\"n\": %d, \"steps\": %d, \"ic\": \"%s\", \"flavour\": \"%s\", \"device_ms\": %.4f, \"g_interactions_per_s\": %.3f, "
                "\"first_call_ms\": %.4f, \"steady_ms_per_step\": %.4f, \"steady_g_interactions_per_s\": %.3f, "
                "\"checksum_x\": %.9e, \"checksum_v\": %.9e, \"launches\": %lld}\n",
-               n, steps, ic.c_str(), host_f3 ? "host-f3" : resident ? "resident" : flavour.c_str(), ms, ms > 0 ? inter / (ms * 1e-3) / 1e9 : 0.0,
+               n, steps, ic.c_str(), gpus > 1 ? "multi-gpu fused exchange" : host_f3 ? "host-f3" : resident ? "resident" : flavour.c_str(), ms, ms > 0 ? inter / (ms * 1e-3) / 1e9 : 0.0,
                ms_first, ms_steady, ms_steady > 0 ? (double)n * (double)n / (ms_steady * 1e-3) / 1e9 : 0.0,
                checksum(bodies, n), checksum(velocity, n), nbody_launch_count());
     }
