@@ -44,6 +44,8 @@ def parse():
     ap.add_argument("--exchange", default="p2p", choices=["nccl", "p2p"],
                     help="multi-GPU position exchange: P2P stores fused into the step's epilogue (default; r1: +0.3%% at N=1M, "
                          "+4.4%% at N=256k on 8 GPUs), or an NCCL all-gather overlapped with the own-slice kernel")
+    ap.add_argument("--barrier", default="auto", choices=["auto", "device", "collective"],
+                    help="fused exchange only: cross-rank barrier inside the step kernel (flags in peer memory) or a 4-byte all-reduce")
     ap.add_argument("--cpu-series", action="store_true",
                     help="with --impl reference: also print baseline B1 of BASELINE.md (reference CPU path at N=1024x10, 16384x3, "
                          "131072x1, -O2 and -O3 builds) as extra JSON lines BEFORE the contract line")
@@ -272,7 +274,7 @@ def run_ours(args):
     if world > 1 and exchange == "p2p":
         # peer mapping needs CUDA IPC + P2P access between all GPUs of the box; agree on it collectively
         try:
-            runner = par.ShardedSimulation(sim, rank, world, device=dev, exchange="p2p")
+            runner = par.ShardedSimulation(sim, rank, world, device=dev, exchange="p2p", barrier=args.barrier)
             ok = torch.ones(1, device=dev)
         except Exception as e:  # noqa: BLE001
             print(f"[bench] rank {rank}: fused exchange unavailable ({e}); using the NCCL all-gather", file=sys.stderr, flush=True)
@@ -392,7 +394,8 @@ def run_ours(args):
                 "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
                 "pct_fp32_peak": round(100 * achieved / peak_tflops, 2),
                 "engine": {"variant": info["variant_name"], "grid_ctas": info["grid_ctas"], "ctas_per_sm": info["ctas_per_sm"],
-                           "exchange": exchange, "autotune": nb.autotune_report()}}
+                           "exchange": exchange, "barrier": getattr(runner, "barrier", None) if exchange == "p2p" else None,
+                           "autotune": nb.autotune_report()}}
         print(json.dumps(line), flush=True)
     sim.close()
     if world > 1:

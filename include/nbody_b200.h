@@ -133,6 +133,14 @@ int nbody_shard_attach_ipc(nbody_ctx* ctx, int peer_rank, const void* handles128
 int nbody_shard_buffers(nbody_ctx* ctx, void** buf0, void** buf1);
 int nbody_shard_attach_ptr(nbody_ctx* ctx, int peer_rank, void* buf0, void* buf1);
 int nbody_shard_step_fused_async(nbody_ctx* ctx, void* stream);
+/* In-kernel barrier for the fused step (choose before the first fused step, the same on every
+ * rank): the step kernel itself waits until every peer has finished the previous step (flags in
+ * this GPU's memory, written by the peers' last CTA with st.release.sys over NVLink) and publishes
+ * its own completion the same way, so a step is ONE launch with no collective call at all.  Only
+ * for one rank per GPU (ranks sharing a GPU would wait on each other).  A wait that sees no
+ * progress for 20 s gives up; nbody_shard_barrier_timeouts() != 0 then means the state is invalid. */
+int nbody_shard_set_device_barrier(nbody_ctx* ctx, int enable);
+int nbody_shard_barrier_timeouts(nbody_ctx* ctx, int* timed_out);
 /* Geometry helper: bytes of one rank's padded slice for (N, world). */
 size_t nbody_shard_slot_bytes(int n_bodies, int world);
 

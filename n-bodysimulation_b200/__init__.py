@@ -74,6 +74,8 @@ SIGNATURES = {
     "nbody_shard_buffers": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp)]),
     "nbody_shard_attach_ptr": (C.c_int, [_vp, C.c_int, _vp, _vp]),
     "nbody_shard_step_fused_async": (C.c_int, [_vp, _vp]),
+    "nbody_shard_set_device_barrier": (C.c_int, [_vp, C.c_int]),
+    "nbody_shard_barrier_timeouts": (C.c_int, [_vp, C.POINTER(C.c_int)]),
     "nbody_step_inplace_f4": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_float, C.c_float]),
     "nbody_step_host_f3": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_double, C.c_double]),
     "nbody_step_opts_default": (C.c_int, [C.POINTER(NBodyStepOpts)]),
@@ -344,6 +346,14 @@ class Simulation:
 
     def shard_attach_ptr(self, peer: int, buf0: int, buf1: int) -> None:
         _check(lib.nbody_shard_attach_ptr(self._h, peer, buf0, buf1))
+
+    def shard_set_device_barrier(self, enable: bool = True) -> None:
+        _check(lib.nbody_shard_set_device_barrier(self._h, int(enable)))
+
+    def shard_barrier_timeouts(self) -> int:
+        t = C.c_int()
+        _check(lib.nbody_shard_barrier_timeouts(self._h, C.byref(t)))
+        return t.value
 
     def shard_step_fused_async(self, stream: int = 0) -> None:
         _check(lib.nbody_shard_step_fused_async(self._h, stream))

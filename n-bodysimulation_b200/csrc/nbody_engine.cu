@@ -170,6 +170,7 @@ const Variant kVariants[] = {
     SVARIANT(86, 8, 512, 1),
 };
 const int kNumVariants = (int)(sizeof kVariants / sizeof kVariants[0]);
+constexpr size_t kFlagBytes = 4096;   // barrier flags behind packed[0]
 constexpr int kSlotAlign = 1024;   // bodies; multiple of every variant's UJ
 
 const Variant* find_variant(int id)
@@ -414,6 +415,12 @@ struct nbody_ctx {
     float4* peer_packed[kMaxPeers + 1][2] = {};
     bool peer_ipc[kMaxPeers + 1] = {};
     int peers_attached = 0;
+    // in-kernel barrier of the fused exchange: flags live behind packed[0] (same allocation, so the peers' IPC
+    // mapping of that buffer reaches them); fused_steps only ever grows, so re-uploads need no flag reset
+    bool device_barrier = false;
+    unsigned long long fused_steps = 0;
+    unsigned* bar_done = nullptr;
+    int* bar_err = nullptr;
 };
 
 namespace {
@@ -507,7 +514,7 @@ void nbody_destroy(nbody_ctx* c)
     if (c->step_graph) cudaGraphExecDestroy(c->step_graph);
     cudaFree(c->X); cudaFree(c->V); cudaFree(c->A); cudaFree(c->accum);
     cudaFree(c->packed[0]); cudaFree(c->packed[1]);
-    cudaFree(c->partial); cudaFree(c->counters); cudaFree(c->energy_part); cudaFree(c->clk); cudaFree(c->stage); cudaFree(c->frame); cudaFree(c->frame_keys);
+    cudaFree(c->partial); cudaFree(c->counters); cudaFree(c->energy_part); cudaFree(c->clk); cudaFree(c->bar_done); cudaFree(c->stage); cudaFree(c->frame); cudaFree(c->frame_keys);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -570,7 +577,10 @@ int nbody_create(nbody_ctx** out, const nbody_params* p)
     TRYCU(cudaMalloc(&c->A, tb));
     TRYCU(cudaMalloc(&c->accum, tb));
     TRYCU(cudaMalloc(&c->stage, (size_t)c->n * sizeof(float4)));
-    TRYCU(cudaMalloc(&c->packed[0], sb));
+    TRYCU(cudaMalloc(&c->packed[0], sb + kFlagBytes));
+    TRYCU(cudaMemset(c->packed[0], 0, sb + kFlagBytes));
+    TRYCU(cudaMalloc(&c->bar_done, 256));
+    TRYCU(cudaMemset(c->bar_done, 0, 256));
     TRYCU(cudaMalloc(&c->packed[1], sb));
     TRYCU(cudaMalloc(&c->partial, partial_bytes));
     TRYCU(cudaMalloc(&c->clk, 4 * sizeof(unsigned long long)));

@@ -316,12 +316,44 @@ int nbody_shard_step_fused_async(nbody_ctx* c, void* stream)
     a.next_src = c->packed[c->cur ^ 1];
     a.next_off = c->p.rank * c->slot_bodies;
     a.maxseg = c->plan_full.maxseg;
-    for (int r = 0; r < c->p.world; ++r)
-        if (r != c->p.rank) a.peer_next[a.n_peer++] = c->peer_packed[r][c->cur ^ 1];
+    const size_t sb = (size_t)c->n_src_pad * sizeof(float4);
+    for (int r = 0; r < c->p.world; ++r) {
+        if (r == c->p.rank) continue;
+        if (c->device_barrier) a.bar_peer_flags[a.n_peer] = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(c->peer_packed[r][0]) + sb);
+        a.peer_next[a.n_peer++] = c->peer_packed[r][c->cur ^ 1];
+    }
+    if (c->device_barrier) {
+        a.bar_flags = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(c->packed[0]) + sb);
+        a.bar_step = c->fused_steps;
+        a.bar_done = c->bar_done;
+        a.bar_err = reinterpret_cast<int*>(c->bar_done) + 16;
+        a.rank = c->p.rank; a.world = c->p.world;
+    }
     rc = launch_force(c->var, c->plan_full, a, st);
     if (rc) return rc;
     c->cur ^= 1;
     ++c->steps_done;
+    ++c->fused_steps;
+    return NBODY_OK;
+}
+
+int nbody_shard_set_device_barrier(nbody_ctx* c, int enable)
+{
+    if (!c) return fail(NBODY_E_INVALID, "null context");
+    if (enable && c->p.world > 1 && c->var->small)
+        return fail(NBODY_E_STATE, "variant %s (small-N family) has no in-kernel barrier; synchronise the ranks from the caller", c->var->name);
+    if (c->fused_steps != 0 && (enable != 0) != c->device_barrier)
+        return fail(NBODY_E_STATE, "the barrier mode must be chosen before the first fused step (every rank the same)");
+    c->device_barrier = enable != 0;
+    return NBODY_OK;
+}
+
+int nbody_shard_barrier_timeouts(nbody_ctx* c, int* timed_out)
+{
+    if (!c || !timed_out) return fail(NBODY_E_INVALID, "null argument");
+    int rc = set_device(c);
+    if (rc) return rc;
+    CU(cudaMemcpy(timed_out, reinterpret_cast<int*>(c->bar_done) + 16, sizeof(int), cudaMemcpyDeviceToHost));
     return NBODY_OK;
 }
 

@@ -42,6 +42,16 @@ struct ForceArgs {
     // (peer memory mapped over NVLink), replacing the all-gather of the new positions
     float4* peer_next[kMaxPeers];
     int n_peer;
+    // in-kernel cross-GPU barrier of the fused exchange (optional; bar_flags == nullptr: the caller
+    // synchronises the ranks between steps).  flags[r] in THIS GPU's memory = number of fused steps rank r
+    // has completed (written by rank r's last CTA with st.release.sys over NVLink).  Step k may read the
+    // peers' positions and overwrite the buffer they read in step k-1 once every flags[r] >= k.
+    unsigned long long* bar_flags;              // local, [world]
+    unsigned long long* bar_peer_flags[kMaxPeers];   // the peers' flag arrays (peer memory)
+    unsigned long long bar_step;                // k: fused steps this rank has completed before this launch
+    unsigned* bar_done;                         // local counter of finished CTAs, zero between launches
+    int* bar_err;                               // set to 1 when a wait timed out (results are then invalid)
+    int rank, world;
     // two-phase accumulation (sharded runs)
     const float4* accum_in;   // added first when non-null
     float4* accum_out;        // when non-null: store sums here, do not integrate
@@ -238,8 +248,22 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
         ++kf;
         return true;
     };
-    if (tid == 0)
+    if (tid == 0) {
+        if (a.bar_flags) {
+            // every source fetch below and every peer store of the epilogue is ordered after this wait (thread 0's
+            // TMA issues -> full barriers -> all consumers).  Polling is local; 20 s without progress = a dead peer.
+            const unsigned long long t0 = globaltimer_ns();
+            for (int r = 0; r < a.world; ++r) {
+                if (r == a.rank) continue;
+                while (ld_acquire_sys_u64(a.bar_flags + r) < a.bar_step) {
+                    if (globaltimer_ns() - t0 > 20000000000ull) { *a.bar_err = 1; break; }
+                    __nanosleep(200);
+                }
+            }
+            __threadfence_system();
+        }
         while (kf < kLookahead && issue()) {}
+    }
 
     const u64 eps2p = pack2(a.eps2, a.eps2);
     int k = 0;   // units consumed so far
@@ -511,6 +535,20 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
         u += (u64)jn;
     }
     if (a.clk && blockIdx.x == 0 && tid == 0) { a.clk[2] = clock64(); a.clk[3] = globaltimer_ns(); }
+    if (a.bar_flags) {
+        // the last CTA of this GPU to get here publishes "step k done" to every peer: all P2P stores of all CTAs
+        // are fenced (system scope) before their CTA counts itself, the publisher fences again before the flags
+        __threadfence_system();
+        __syncthreads();
+        if (tid == 0) {
+            const unsigned old = atomicAdd(a.bar_done, 1u);
+            if (old == gridDim.x - 1) {
+                *a.bar_done = 0u;
+                __threadfence_system();
+                for (int p = 0; p < a.n_peer; ++p) st_release_sys_u64(a.bar_peer_flags[p] + a.rank, a.bar_step + 1);
+            }
+        }
+    }
     if (CS > 1) cluster_sync_all();   // no CTA leaves while peers may still touch its shared memory
 }
 

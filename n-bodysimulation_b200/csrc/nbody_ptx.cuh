@@ -55,6 +55,18 @@ __device__ __forceinline__ unsigned long long globaltimer_ns()
     return t;
 }
 
+// ---- system-scope flags (cross-GPU barrier of the fused exchange) ---------------------------
+__device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long* p)
+{
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys_u64(unsigned long long* p, unsigned long long v)
+{
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
 // ---- shared memory ------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p)
 {

@@ -43,7 +43,8 @@ class ShardedSimulation:
     object with shard_local_async / shard_remote_async / shard_sources (the gloo CPU test
     passes a host-memory stand-in).  `group` is a torch.distributed process group."""
 
-    def __init__(self, sim, rank: int, world: int, group=None, device=None, overlap: bool = True, exchange: str = "nccl"):
+    def __init__(self, sim, rank: int, world: int, group=None, device=None, overlap: bool = True, exchange: str = "nccl",
+                 barrier: str = "auto"):
         import torch
         import torch.distributed as dist
         self.torch, self.dist = torch, dist
@@ -66,6 +67,29 @@ class ShardedSimulation:
                 if r != rank:
                     sim.shard_attach_ipc(r, handles[r])
             self._flag = torch.zeros(1, dtype=torch.int32, device=device if device is not None else "cpu")
+            # cross-rank barrier between fused steps: inside the step kernel itself (flags in peer memory, no
+            # collective call per step) where the engine offers it, else a 4-byte all-reduce on the step's stream
+            assert barrier in ("auto", "device", "collective")
+            self.barrier = "collective"
+            on_gpu = device is not None and torch.device(device).type == "cuda"
+            if barrier != "collective" and on_gpu and hasattr(sim, "shard_set_device_barrier"):
+                try:
+                    sim.shard_set_device_barrier(True)
+                    ok = 1
+                except Exception:  # noqa: BLE001  (small-N family kernels have no in-kernel barrier)
+                    ok = 0
+                agree = torch.tensor([ok], dtype=torch.int32, device=device)
+                dist.all_reduce(agree, op=dist.ReduceOp.MIN, group=group)
+                if int(agree.item()) == 1:
+                    self.barrier = "device"
+                elif ok:
+                    sim.shard_set_device_barrier(False)
+                if barrier == "device" and self.barrier != "device":
+                    raise RuntimeError("in-kernel barrier not available on every rank")
+            # nobody steps before everybody has uploaded and attached
+            dist.all_reduce(self._flag, group=group)
+            if on_gpu:
+                torch.cuda.synchronize(device)
 
     def _source_views(self, which: int):
         ptr, total, slot = self.sim.shard_sources(which)
@@ -100,8 +124,9 @@ class ShardedSimulation:
             else:
                 st = self.compute if self.overlap else torch.cuda.current_stream(self.device)
                 self.sim.shard_step_fused_async(st.cuda_stream)
-                with torch.cuda.stream(st):
-                    self.dist.all_reduce(self._flag, group=self.group)
+                if self.barrier != "device":
+                    with torch.cuda.stream(st):
+                        self.dist.all_reduce(self._flag, group=self.group)
             self.steps_done += 1
             return
         if not self.overlap:

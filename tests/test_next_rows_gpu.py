@@ -244,7 +244,7 @@ def test_large_contexts_pick_their_kernel_by_measurement(cuda, nb):
     chosen = [k for k in cands if nb.variants()[int(k)].split(":")[0] == name]
     assert len(chosen) == 1
     # the report rounds to 1 us: the chosen kernel is the fastest up to that rounding
-    assert float(cands[chosen[0]][:-2]) <= min(float(ms[:-2]) for ms in cands.values()) + 0.0015, rep
+    assert float(cands[chosen[0]][:-2]) <= min(float(ms[:-2]) for ms in cands.values()) * 1.005 + 0.0015, rep
 
 
 def test_mid_size_contexts_pick_tile_shape_by_unit_balance(cuda, nb, oracle):

@@ -28,6 +28,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--bodies", type=int, default=100003)
 ap.add_argument("--steps", type=int, default=1)
 ap.add_argument("--exchange", default="nccl")
+ap.add_argument("--barrier", default="auto")
 args = ap.parse_args()
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local)
@@ -37,11 +38,12 @@ n = args.bodies
 x0 = nb.ic_uniform(n, seed=77)
 sim = nb.Simulation(n, rank=rank, world=world, device=local)
 sim.upload(x0)
-runner = par.ShardedSimulation(sim, rank, world, device=dev, exchange=args.exchange)
+runner = par.ShardedSimulation(sim, rank, world, device=dev, exchange=args.exchange, barrier=args.barrier)
 for _ in range(args.steps):
     runner.step()
 runner.synchronize()
 x, v, a = sim.download()
+sim_timeouts = sim.shard_barrier_timeouts() if world > 1 else 0
 per = sim.count if rank == 0 else None
 parts = [None] * world
 dist.all_gather_object(parts, (sim.begin, x, v, a))
@@ -58,7 +60,7 @@ if rank == 0:
 
     def err(p, q):
         return float(np.max(np.linalg.norm((p - q)[:, :3].astype(np.float64), axis=1) / np.maximum(np.linalg.norm(q[:, :3].astype(np.float64), axis=1), 1e-300)))
-    res = {"world": world, "exchange": args.exchange, "n": n, "steps": args.steps, "bodies_gathered": int(len(X)),
+    res = {"world": world, "exchange": args.exchange, "barrier": getattr(runner, "barrier", None), "barrier_timeouts": sim_timeouts, "n": n, "steps": args.steps, "bodies_gathered": int(len(X)),
            "err_x": err(X, xr), "err_v": err(V, vr), "err_a": err(A, ar)}
     res["spread_a_1gpu"], res["spread_v_1gpu"], res["spread_x_1gpu"] = err(a2, ar), err(v2, vr), err(x2, xr)
     tol_a, tol_v, tol_x = max(1e-5, 2 * res["spread_a_1gpu"]), max(1e-5, 2 * res["spread_v_1gpu"]), max(1e-6, 2 * res["spread_x_1gpu"])
