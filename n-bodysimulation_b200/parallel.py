@@ -12,9 +12,11 @@ interactions against the rank's own slice:
 `exchange="p2p"` replaces the gather by a FUSED exchange: every rank maps its peers' source
 buffers (CUDA IPC handles passed around with all_gather_object) and the step kernel's epilogue
 stores each new position straight into every rank's next buffer over NVLink -- one kernel per
-step over all sources, then a 4-byte all-reduce on the same stream as the cross-rank barrier:
+step over all sources.  The cross-rank barrier between steps is inside the kernel (flags in peer
+memory; `barrier="device"`, chosen by "auto" when every rank has its own GPU) or a 4-byte all-reduce
+on the same stream (`barrier="collective"`):
 
-    compute stream :  fused step (own targets x all sources; epilogue -> own + peers' next buffers) | barrier
+    compute stream :  fused step (own targets x all sources; epilogue -> own + peers' next buffers) [| all-reduce]
 
 Body order and slot geometry come from the C ABI (nbody_shard_sources): rank r's
 slice sits at byte offset r*slot_bytes of the packed source buffer, so the
@@ -38,6 +40,13 @@ def as_tensor(ptr: int, nbytes: int, device):
     return torch.as_tensor(DevBuf(ptr, nbytes), device=device)
 
 
+def _device_identity(torch, device):
+    """(host, GPU uuid): equal on two ranks exactly when they run on the same physical GPU"""
+    import socket
+    props = torch.cuda.get_device_properties(device)
+    return (socket.gethostname(), str(getattr(props, "uuid", torch.device(device).index)))
+
+
 class ShardedSimulation:
     """Steps a sharded run.  `sim` is this rank's nb.Simulation(rank=r, world=G) -- or any
     object with shard_local_async / shard_remote_async / shard_sources (the gloo CPU test
@@ -57,22 +66,25 @@ class ShardedSimulation:
             self.comm = torch.cuda.Stream(device=device)
         self.steps_done = 0
         assert exchange in ("nccl", "p2p")
+        assert barrier in ("auto", "device", "collective")
         self.exchange = exchange if world > 1 else "nccl"
+        self.barrier = None
         if self.exchange == "p2p":
+            on_gpu = device is not None and torch.device(device).type == "cuda"
             # every rank opens every other rank's two source buffers (cudaIpcOpenMemHandle)
-            mine = sim.shard_ipc_handles()
-            handles = [None] * world
-            dist.all_gather_object(handles, mine, group=group)
+            mine = (sim.shard_ipc_handles(), _device_identity(torch, device) if on_gpu else None)
+            got = [None] * world
+            dist.all_gather_object(got, mine, group=group)
             for r in range(world):
                 if r != rank:
-                    sim.shard_attach_ipc(r, handles[r])
+                    sim.shard_attach_ipc(r, got[r][0])
+            # kernels that wait for each other must not share a GPU
+            own_gpu_each = on_gpu and len({g[1] for g in got}) == world
             self._flag = torch.zeros(1, dtype=torch.int32, device=device if device is not None else "cpu")
             # cross-rank barrier between fused steps: inside the step kernel itself (flags in peer memory, no
             # collective call per step) where the engine offers it, else a 4-byte all-reduce on the step's stream
-            assert barrier in ("auto", "device", "collective")
             self.barrier = "collective"
-            on_gpu = device is not None and torch.device(device).type == "cuda"
-            if barrier != "collective" and on_gpu and hasattr(sim, "shard_set_device_barrier"):
+            if barrier != "collective" and own_gpu_each and hasattr(sim, "shard_set_device_barrier"):
                 try:
                     sim.shard_set_device_barrier(True)
                     ok = 1
@@ -84,8 +96,8 @@ class ShardedSimulation:
                     self.barrier = "device"
                 elif ok:
                     sim.shard_set_device_barrier(False)
-                if barrier == "device" and self.barrier != "device":
-                    raise RuntimeError("in-kernel barrier not available on every rank")
+            if barrier == "device" and self.barrier != "device":
+                raise RuntimeError("in-kernel barrier needs every rank on its own GPU and a kernel family that has it")
             # nobody steps before everybody has uploaded and attached
             dist.all_reduce(self._flag, group=group)
             if on_gpu:

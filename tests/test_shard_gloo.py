@@ -158,6 +158,12 @@ def _worker_p2p(rank, world, port, n, steps, out_dir):
     dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
     sim = SharedMemStandIn(nb, oracle, nb.ic_uniform(n, seed=99), rank, world)
     runner = par.ShardedSimulation(sim, rank, world, device=None, exchange="p2p")
+    assert runner.barrier == "collective"                        # no GPUs: "auto" must not pick the in-kernel barrier
+    try:
+        par.ShardedSimulation(SharedMemStandIn.__new__(SharedMemStandIn), rank, world, device=None, exchange="nccl", barrier="bogus")
+        raise SystemExit("bad barrier name accepted")
+    except AssertionError:
+        pass
     for _ in range(steps):
         runner.step()                                            # ends with the all-reduce barrier
     assert sim.calls == ["fused"] * steps
