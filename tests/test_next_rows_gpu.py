@@ -215,6 +215,42 @@ def test_fused_exchange_on_one_gpu_matches_unsharded(cuda, nb, oracle, world):
     assert oracle.norm_rel_err(a, ar) <= 3e-6 and oracle.norm_rel_err(x, xr) <= 1e-6 and oracle.norm_rel_err(v, vr) <= 3e-6
 
 
+def test_in_kernel_barrier_between_two_gpus(cuda, nb, oracle):
+    # the cross-GPU form of the barrier: each rank on its OWN device (kernels that wait for each other must not
+    # share a GPU), all steps enqueued back to back with no host synchronisation and no collective in between
+    torch = cuda
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (tools/verify_sharded.py --barrier device covers it under torchrun)")
+    # moving bodies (Plummer sphere with velocities): a rank that read a peer's slot one step early or late
+    # would be off by |v| dt / r ~ 1e-2 in the accelerations, far above the rounding-level tolerance below
+    n, steps = 40001, 6
+    x0, v0 = nb.ic_plummer(n, seed=5)
+    with nb.Simulation(n, dt=0.02) as ref:
+        ref.upload(x0, v0).step(steps)
+        xr, vr, ar = ref.download()
+    sims = [nb.Simulation(n, dt=0.02, rank=r, world=2, device=r) for r in range(2)]
+    try:
+        for s in sims:
+            s.upload(x0, v0)
+        sims[0].shard_attach_ptr(1, *sims[1].shard_buffers())
+        sims[1].shard_attach_ptr(0, *sims[0].shard_buffers())
+        for s in sims:
+            s.shard_set_device_barrier(True)
+        for _ in range(steps):
+            for s in sims:
+                s.shard_step_fused_async()
+        parts = [s.download() for s in sims]
+        assert [s.shard_barrier_timeouts() for s in sims] == [0, 0]
+        with pytest.raises(nb.NBodyError):
+            sims[0].shard_set_device_barrier(False)            # not once fused steps have run with it
+    finally:
+        for s in sims:
+            s.close()
+    x = np.concatenate([p[0] for p in parts]); v = np.concatenate([p[1] for p in parts]); a = np.concatenate([p[2] for p in parts])
+    errs = (oracle.norm_rel_err(x, xr), oracle.norm_rel_err(v, vr), oracle.norm_rel_err(a, ar))
+    assert errs[0] <= 1e-5 and errs[1] <= 1e-4 and errs[2] <= 1e-4, errs
+
+
 # ---- launch-bound step loops: CUDA-graph replay gives the same bits as step-by-step launches ---------------
 @pytest.mark.parametrize("n", [777, 5000])
 def test_graph_replayed_steps_equal_single_steps(cuda, nb, n):
