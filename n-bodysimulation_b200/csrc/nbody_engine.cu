@@ -182,7 +182,6 @@ const Variant* find_variant(int id)
 
 int tuned_large_variant(int n_sources);
 int mid_variant(int n_targets, int n_sources);
-constexpr int kSlotAlignBodies = 1024;   // = kSlotAlign below
 
 int auto_variant(int n_targets, int n_sources)
 {
@@ -208,7 +207,7 @@ int mid_variant(int n_targets, int n_sources)
     static const Cand cands[] = {{90, 6, 256}, {112, 6, 128}, {113, 6, 64}, {93, 8, 256}, {110, 8, 128}, {111, 8, 64}};
     int dev = 0, sms = 148;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const long long src_pad = (long long)(n_sources + kSlotAlignBodies - 1) / kSlotAlignBodies * kSlotAlignBodies;
+    const long long src_pad = (long long)(n_sources + kSlotAlign - 1) / kSlotAlign * kSlotAlign;
     double best_cost = 1e300;
     int best = 90;
     for (const Cand& c : cands) {
@@ -304,8 +303,8 @@ int launch_pack(const float4* X, int n, float4* packed, int off, int n_cover, cu
 }
 
 // ---- which of the equivalent large-N kernels is fastest on this device ---------------------------------
-// Variants 45/90/91 (T6) and 21/92/93/96 (T8) issue the same instructions per interaction and differ
-// only in source order, i.e. in the register allocation ptxas happens to give them; measured, that is
+// The candidates below (T6 with 256- or 512-body units, one T8) issue the same instructions per interaction and
+// differ only in source order, i.e. in the register allocation ptxas happens to give them; measured, that is
 // worth +-3.5 % (register-bank conflicts on the 3-operand FFMA2; profiles/r1_variant_sweep_*).  Rather
 // than trust one allocation, the first large context of a process times each candidate for ~1 ms on
 // synthetic bodies and keeps the fastest (NBODY_LARGE_VARIANT=<id> in the environment overrides).
@@ -419,8 +418,7 @@ struct nbody_ctx {
     // mapping of that buffer reaches them); fused_steps only ever grows, so re-uploads need no flag reset
     bool device_barrier = false;
     unsigned long long fused_steps = 0;
-    unsigned* bar_done = nullptr;
-    int* bar_err = nullptr;
+    unsigned* bar_done = nullptr;                // 256 B: [0] CTA arrival counter, [16] time-out mark
 };
 
 namespace {
