@@ -10,7 +10,12 @@
  * bit-for-bit against (a) the reference's own validation.cpp / utils.cpp object
  * code compiled unchanged into oracle/_ref/libref_cpu.so (when present) and
  * (b) the golden vectors in tests/golden/ that were generated from that
- * object code by tests/golden/make_golden.py.
+ * object code by tests/golden/make_golden.py.  The two flavours the reference
+ * has as GPU code only (oracle_step_headless_f3, oracle_step_mixed) are checked
+ * against the output of the reference's kernels on a B200
+ * (tests/golden/headless_ref_gpu.npz), to summation rounding.  The point-splat
+ * frame (oracle_render) restates shader + fixed-function arithmetic and stays
+ * UNPINNED: no OpenGL implementation exists on these machines.
  *
  * Build:  gcc -O2 -ffp-contract=off -fopenmp -shared -fPIC  (see oracle/Makefile)
  * -ffp-contract=off keeps every multiply and add separately rounded, which is
@@ -235,9 +240,11 @@ int oracle_num_threads(void)
  * inter_block_reduction: `v += 0.5 * DT * a` evaluates in DOUBLE (0.5 is a
  * double literal, DT a float macro) and rounds once; `x += DT * v` is float
  * and -- that code exists only as GPU code, built by nvcc with its default
- * -fmad=true -- one fused multiply-add.  PARITY UNPINNED for this flavour:
- * the reference has no CPU twin of it and it cannot run here (it needs an
- * OpenGL-mapped buffer); only the pair sum is pinned (shared with O2).
+ * -fmad=true -- one fused multiply-add.  PINNED on the reference kernels'
+ * own output on a B200 (tests/golden/headless_ref_gpu.npz, made by
+ * tests/golden/make_golden_headless_gpu.py through oracle/ref_reduction_glue.cu,
+ * which replaces only the OpenGL-bound launch sequence): agreement to summation
+ * rounding, <= 4.4e-6 per-body norm-relative at N <= 2048.
  * V, A: float[stride*N], stride 4 (float4, A.w = 0) or 3 (float3). */
 void oracle_step_mixed(float *X, float *A, float *V, int N, float eps2, float dt, int stride)
 {

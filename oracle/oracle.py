@@ -141,7 +141,8 @@ def norm_rel_err(a, b):
 
 def step_mixed(X, A, V, eps2=0.002, dt=0.1):
     """reduction flavours (kernel.cu:406-436 / :439-469): double half-kick, float FMA drift.
-    V, A are (N,4) or (N,3) float32.  Parity unpinned (GPU-only reference code)."""
+    V, A are (N,4) or (N,3) float32.  Pinned on the reference kernels' output on a B200
+    (tests/golden/headless_ref_gpu.npz)."""
     stride = V.shape[1]
     assert A.shape[1] == stride and stride in (3, 4)
     _lib.oracle_step_mixed(_fp(X), _fp(A), _fp(V), len(X), C.c_float(eps2), C.c_float(dt), C.c_int(stride))

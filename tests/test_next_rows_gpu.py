@@ -82,6 +82,27 @@ def test_embparallel_float4_matches_the_reduction_flavour_oracle(cuda, nb, oracl
     assert np.all(a[:, 3] == 0) and np.array_equal(x[:, 3], x0[:, 3])        # kernel.cu:409,433-435
 
 
+@pytest.mark.parametrize("stride", [4, 3])
+@pytest.mark.parametrize("n", [1024, 2048])
+def test_embparallel_against_the_reference_kernels_output(cuda, nb, oracle, golden, n, stride):
+    # golden = the reference's kernel_reduction[_float3] + inter_block_reduction[_float3] run on a B200
+    # (tests/golden/make_golden_headless_gpu.py)
+    torch = cuda
+    g, k = golden["headless_ref_gpu"], f"red4_%s_n{n}"    # the float3 twin's xyz bits are the same (stored once)
+    x0 = oracle.ic_reference(n)
+    ref = lambda key: g[k % key][:, :stride] if key[0] != "x" else x0 + g["d_" + k % key]   # noqa: E731
+    dx = torch.from_numpy(x0).cuda()
+    dv, da = torch.zeros(n * stride, device="cuda"), torch.zeros(n * stride, device="cuda")
+    step = nb.simulateHeadless_embParallel if stride == 4 else nb.simulateHeadless_embParallel_float3
+    step(dx, da, dv, None, n)
+    got = lambda t: t.cpu().numpy().reshape(n, -1)   # noqa: E731
+    assert oracle.norm_rel_err(got(da), ref("a1")) <= TOL_A and oracle.norm_rel_err(got(dv), ref("v1")) <= TOL_V
+    assert oracle.norm_rel_err(got(dx), ref("x1")) <= TOL_X
+    for _ in range(int(g["steps"]) - 1):
+        step(dx, da, dv, None, n)
+    assert oracle.norm_rel_err(got(dv), ref("vk")) <= TOL_V and oracle.norm_rel_err(got(dx), ref("xk")) <= TOL_X
+
+
 def test_embparallel_float3_layout(cuda, nb, oracle):
     torch = cuda
     for n in (1, 31, 2049):

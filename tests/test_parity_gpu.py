@@ -106,6 +106,19 @@ def test_host_pointer_float3_flavour(cuda, nb, oracle):
     assert oracle.norm_rel_err(xb, X) <= TOL_X and oracle.norm_rel_err(vb, V3) <= 2 * TOL_V
 
 
+@pytest.mark.parametrize("n", [1024, 4096])
+def test_host_pointer_float3_flavour_against_the_reference_kernel_output(cuda, nb, oracle, golden, n):
+    # golden = the reference's own headless kernel (Sim-Without-OpenGL-Integration/kernel.cu) run on a B200
+    g = golden["headless_ref_gpu"]
+    x0 = oracle.ic_reference(n, max_w=1e8)                          # positions are stored as differences from these
+    xb, vb, ab = x0.copy(), np.zeros((n, 3), np.float32), np.zeros((n, 3), np.float32)
+    nb.simulate_host_f3(xb, ab, vb, n)
+    assert oracle.norm_rel_err(vb, g[f"v1_n{n}"]) <= TOL_V and oracle.norm_rel_err(xb, x0 + g[f"d_x1_n{n}"]) <= TOL_X
+    for _ in range(int(g["steps"]) - 1):
+        nb.simulate_host_f3(xb, ab, vb, n)
+    assert oracle.norm_rel_err(vb, g[f"vk_n{n}"]) <= TOL_V and oracle.norm_rel_err(xb, x0 + g[f"d_xk_n{n}"]) <= TOL_X
+
+
 def test_deterministic_and_exactly_linear_in_mass(cuda, nb):
     n = 40000
     x0 = nb.ic_uniform(n, seed=5)
