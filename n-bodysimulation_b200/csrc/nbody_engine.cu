@@ -17,6 +17,8 @@
 #include <utility>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>   // header-only NVTX v3: a no-op unless a tool (nsys, ncu --nvtx) is attached
+
 #include "../../include/nbody_b200.h"
 #include "nbody_kernels.cuh"
 
@@ -37,6 +39,15 @@ int fail(int code, const char* fmt, ...)
     g_err = buf;
     return code;
 }
+
+// named range around an API call, for timelines (the reference has no tracing at all)
+struct TraceRange {
+    explicit TraceRange(const char* name) { nvtxRangePushA(name); }
+    ~TraceRange() { nvtxRangePop(); }
+    TraceRange(const TraceRange&) = delete;
+    TraceRange& operator=(const TraceRange&) = delete;
+};
+#define TRACE_CALL() TraceRange trace_range_(__func__)
 
 #define CU(call)                                                                          \
     do {                                                                                  \
@@ -521,6 +532,7 @@ void nbody_destroy(nbody_ctx* c)
 
 int nbody_create(nbody_ctx** out, const nbody_params* p)
 {
+    TRACE_CALL();
     if (!out || !p) return fail(NBODY_E_INVALID, "null argument");
     *out = nullptr;
     if (p->n_bodies <= 0) return fail(NBODY_E_INVALID, "n_bodies must be > 0 (got %d)", p->n_bodies);

@@ -56,6 +56,7 @@ extern "C" {
 
 int nbody_upload(nbody_ctx* c, const float* x4, const float* v4)
 {
+    TRACE_CALL();
     if (!c || !x4) return fail(NBODY_E_INVALID, "null argument");
     int rc = set_device(c);
     if (rc) return rc;
@@ -85,6 +86,7 @@ int nbody_upload(nbody_ctx* c, const float* x4, const float* v4)
 
 int nbody_download(nbody_ctx* c, float* x4, float* v4, float* a4)
 {
+    TRACE_CALL();
     if (!c) return fail(NBODY_E_INVALID, "null context");
     int rc = set_device(c);
     if (rc) return rc;
@@ -98,6 +100,7 @@ int nbody_download(nbody_ctx* c, float* x4, float* v4, float* a4)
 
 int nbody_step_async(nbody_ctx* c, int nsteps)
 {
+    TRACE_CALL();
     if (!c) return fail(NBODY_E_INVALID, "null context");
     if (nsteps < 0) return fail(NBODY_E_INVALID, "nsteps must be >= 0");
     if (c->p.world != 1) return fail(NBODY_E_STATE, "nbody_step on a sharded context; use nbody_shard_*");
@@ -130,6 +133,7 @@ int nbody_step_async(nbody_ctx* c, int nsteps)
 
 int nbody_sync(nbody_ctx* c)
 {
+    TRACE_CALL();
     if (!c) return fail(NBODY_E_INVALID, "null context");
     int rc = set_device(c);
     if (rc) return rc;
@@ -168,6 +172,7 @@ int nbody_kernel_clock_mhz(nbody_ctx* c, float* mhz)
 
 int nbody_energy(nbody_ctx* c, double* ke, double* pe)
 {
+    TRACE_CALL();
     if (!c || !ke || !pe) return fail(NBODY_E_INVALID, "null argument");
     if (c->p.world != 1) return fail(NBODY_E_STATE, "nbody_energy needs an unsharded context");
     int rc = set_device(c);
@@ -200,6 +205,7 @@ int nbody_shard_sources(nbody_ctx* c, int which, void** dptr, size_t* total_byte
 
 int nbody_shard_local_async(nbody_ctx* c, void* stream)
 {
+    TRACE_CALL();
     if (!c) return fail(NBODY_E_INVALID, "null context");
     int rc = set_device(c);
     if (rc) return rc;
@@ -215,6 +221,7 @@ int nbody_shard_local_async(nbody_ctx* c, void* stream)
 
 int nbody_shard_remote_async(nbody_ctx* c, void* stream)
 {
+    TRACE_CALL();
     if (!c) return fail(NBODY_E_INVALID, "null context");
     int rc = set_device(c);
     if (rc) return rc;
@@ -305,6 +312,7 @@ int nbody_shard_buffers(nbody_ctx* c, void** buf0, void** buf1)
 
 int nbody_shard_step_fused_async(nbody_ctx* c, void* stream)
 {
+    TRACE_CALL();
     if (!c) return fail(NBODY_E_INVALID, "null context");
     int rc = set_device(c);
     if (rc) return rc;
@@ -431,6 +439,7 @@ extern "C" {
 
 int nbody_step_inplace_f4(float* d_bodies4, float* d_accel4, float* d_vel4, int n, float eps2, float dt)
 {
+    TRACE_CALL();
     if (!d_bodies4 || !d_accel4 || !d_vel4) return fail(NBODY_E_INVALID, "null device pointer");
     if (n <= 0) return fail(NBODY_E_INVALID, "N must be > 0 (got %d)", n);
     if (!(eps2 > 0.f)) return fail(NBODY_E_INVALID, "eps2 must be > 0");
@@ -446,6 +455,7 @@ int nbody_step_inplace_f4(float* d_bodies4, float* d_accel4, float* d_vel4, int 
 
 int nbody_step_host_f3(float* h_bodies4, float* h_accel3, float* h_vel3, int n, double eps2, double dt)
 {
+    TRACE_CALL();
     (void)h_accel3;   // never copied back by the reference either (headless kernel.cu:115-124)
     if (!h_bodies4 || !h_vel3) return fail(NBODY_E_INVALID, "null host pointer");
     if (n <= 0) return fail(NBODY_E_INVALID, "N must be > 0 (got %d)", n);
@@ -479,6 +489,7 @@ int nbody_step_opts_default(nbody_step_opts* o)
 
 int nbody_step_inplace_opts(float* d_bodies4, void* d_accel, void* d_vel, int n, const nbody_step_opts* o)
 {
+    TRACE_CALL();
     if (!d_bodies4 || !d_accel || !d_vel || !o) return fail(NBODY_E_INVALID, "null pointer");
     if (n <= 0) return fail(NBODY_E_INVALID, "N must be > 0 (got %d)", n);
     if (!(o->eps2 > 0.f)) return fail(NBODY_E_INVALID, "eps2 must be > 0");

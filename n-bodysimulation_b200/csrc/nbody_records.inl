@@ -43,6 +43,7 @@ int nbody_steps_done(nbody_ctx* c, long long* steps)
 
 int nbody_snapshot_save(nbody_ctx* c, const char* path)
 {
+    TRACE_CALL();
     if (!c || !path) return fail(NBODY_E_INVALID, "null argument");
     if (c->p.world != 1) return fail(NBODY_E_STATE, "nbody_snapshot_save needs an unsharded context (gather the shards with nbody_download first)");
     int rc = set_device(c);
@@ -67,6 +68,7 @@ int nbody_snapshot_save(nbody_ctx* c, const char* path)
 
 int nbody_snapshot_load(nbody_ctx* c, const char* path)
 {
+    TRACE_CALL();
     if (!c || !path) return fail(NBODY_E_INVALID, "null argument");
     FILE* f = fopen(path, "rb");
     if (!f) return fail(NBODY_E_INVALID, "cannot open %s", path);

@@ -136,6 +136,7 @@ int nbody_view_default(nbody_view* v)
 
 int nbody_render_device(const float* d_bodies4, int n, const nbody_view* v, unsigned char* d_rgba)
 {
+    TRACE_CALL();
     if (!d_bodies4 || !d_rgba) return fail(NBODY_E_INVALID, "null argument");
     if (n <= 0) return fail(NBODY_E_INVALID, "N must be > 0 (got %d)", n);
     int rc = check_view(v);
@@ -159,6 +160,7 @@ int nbody_render_device(const float* d_bodies4, int n, const nbody_view* v, unsi
 
 int nbody_render(nbody_ctx* c, const nbody_view* v, unsigned char* h_rgba)
 {
+    TRACE_CALL();
     if (!c || !h_rgba) return fail(NBODY_E_INVALID, "null argument");
     if (c->p.world != 1) return fail(NBODY_E_STATE, "nbody_render needs an unsharded context (a shard holds only its own bodies)");
     int rc = check_view(v);

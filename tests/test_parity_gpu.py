@@ -225,8 +225,12 @@ def test_sharded_contexts_on_one_gpu_match_unsharded(cuda, nb, oracle, world):
 
 def _problem_counts(binary, steps):
     """lines printed by the reference's verify_still_bodies (validation.cpp:143-164) per array"""
+    import os
     import subprocess
-    out = subprocess.run([binary, str(steps)], capture_output=True, text=True, timeout=300, check=True).stdout
+    # one host thread: the reference's CPU_compute updates positions in place inside its OpenMP loop (SURVEY F4), so
+    # with several threads its result -- and with it these counts -- changes from run to run
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    out = subprocess.run([binary, str(steps)], capture_output=True, text=True, timeout=300, check=True, env=env).stdout
     counts, sec = {}, None
     for line in out.splitlines():
         if line.startswith("=="):
@@ -249,6 +253,8 @@ def test_reference_checker_objects_accept_our_simulate_as_they_accept_their_own_
         pytest.skip("oracle/_ref binaries were not built (they need /root/reference at build time)")
     for steps in (1, 10):
         a, b = _problem_counts(ours, steps), _problem_counts(own, steps)
-        assert a["positions"] <= b["positions"] + 2, (steps, a, b)
-        assert a["velocities"] <= 1.1 * b["velocities"] + 2 and a["accelerations"] <= 1.1 * b["accelerations"] + 2, (steps, a, b)
+        # the reference's kernel races on the positions between blocks (F5), so its own count is not a constant:
+        # allow three standard deviations of a count that size on top of it
+        for key, factor in (("positions", 1.0), ("velocities", 1.1), ("accelerations", 1.1)):
+            assert a[key] <= factor * b[key] + 3 * b[key] ** 0.5 + 2, (steps, key, a, b)
     assert a["positions"] < 0.01 * 8192                      # 10 steps: > 99 % of the bodies within the reference's own 1 %
