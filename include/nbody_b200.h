@@ -220,6 +220,12 @@ int nbody_variant_id(int index);
  * allocation ptxas gave each is worth +-3.5 %, so the engine measures instead of
  * guessing.  Environment NBODY_LARGE_VARIANT=<id> forces the choice. */
 int nbody_autotune_report(char* buf, size_t buflen);
+/* The kernel variant NBODY_VARIANT_AUTO resolves to for a context owning n_targets of n_sources
+ * bodies on a device with sm_count SMs, by the static rules alone (small-N family below 12 288
+ * sources, tile shape x unit size by unit balance up to 65 536, one of the measured candidates
+ * above -- for that last case the id returned is the first candidate and *measured is set to 1:
+ * the real choice is timed on the device).  Host-only; needs no GPU. */
+int nbody_choose_variant(int n_targets, int n_sources, int sm_count, int* measured);
 /* Variant / grid actually used by ctx (after AUTO resolution). */
 int nbody_ctx_info(nbody_ctx* ctx, int* variant, int* grid_ctas, int* ctas_per_sm, int* sm_count);
 

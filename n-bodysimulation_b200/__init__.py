@@ -93,6 +93,7 @@ SIGNATURES = {
     "nbody_launch_count": (C.c_longlong, []),
     "nbody_variant_info": (C.c_int, [C.c_int, C.c_char_p, C.c_size_t]),
     "nbody_variant_id": (C.c_int, [C.c_int]),
+    "nbody_choose_variant": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]),
     "nbody_autotune_report": (C.c_int, [C.c_char_p, C.c_size_t]),
     "nbody_ctx_info": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "nbody_ic_uniform": (C.c_int, [_vp, C.c_int, C.c_ulonglong, C.c_float, C.c_float, C.c_float]),
@@ -137,6 +138,16 @@ def variants() -> dict:
         lib.nbody_variant_info(i, buf, 320)
         out[i] = buf.value.decode()
     return out
+
+
+def choose_variant(n_targets: int, n_sources: int, sm_count: int = 148):
+    """(variant id, measured) NBODY_VARIANT_AUTO resolves to by the static rules; measured = True: one of the
+    equivalent large-N kernels, timed on the device when the first such context is created.  Host-only."""
+    m = C.c_int(0)
+    vid = lib.nbody_choose_variant(n_targets, n_sources, sm_count, C.byref(m))
+    if vid == 0:
+        raise NBodyError(f"[-1] {lib.nbody_last_error().decode()}")   # NBODY_E_INVALID
+    return vid, bool(m.value)
 
 
 def autotune_report() -> str:

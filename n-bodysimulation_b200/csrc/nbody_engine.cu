@@ -192,32 +192,44 @@ const Variant* find_variant(int id)
 }
 
 int tuned_large_variant(int n_sources);
-int mid_variant(int n_targets, int n_sources);
+int mid_variant(int n_targets, int n_sources, int sms);
 
-int auto_variant(int n_targets, int n_sources)
+// The static part of the choice (best of the r1 sweeps, profiles/r1_variant_sweep_*.jsonl; the cluster variants
+// 60-70 measured neutral (C2 multicast) or slower (C4/C8, DSMEM j-split) and are opt-in only).
+// *measured = true: one of the equivalent large-N kernels, to be picked by tuned_large_variant().
+int static_variant(int n_targets, int n_sources, int sms, bool* measured)
 {
-    // best of the r1 sweeps (profiles/r1_variant_sweep_*.jsonl); the cluster variants (60-70)
-    // measured neutral (C2 multicast) or slower (C4/C8, DSMEM j-split) and are opt-in only
+    *measured = false;
     if (n_sources < 12288) {             // a step is < 50 us: latency decides -> small-N family
         if (n_sources < 3072) return 85; // 2 targets / CTA, sources split over 128 threads, shuffle reduction
         return 82;                       // 4 targets / CTA
     }
-    if (n_targets >= 12288 && n_sources < 65536) return mid_variant(n_targets, n_sources);
-    if (n_targets >= 12288) return tuned_large_variant(n_sources);
+    if (n_targets >= 12288 && n_sources < 65536) return mid_variant(n_targets, n_sources, sms);
+    if (n_targets >= 12288) { *measured = true; return 45; }
     if (n_targets >= 2048) return 3;     // T2 x 256 threads, 3 CTAs/SM
     return 12;                           // T1 x 128 threads, 64-body units
+}
+
+int auto_variant(int n_targets, int n_sources)
+{
+    bool measured = false;
+    const int id = static_variant(n_targets, n_sources, 0, &measured);
+    return measured ? tuned_large_variant(n_sources) : id;
 }
 
 // Mid-size N (12 k ... 64 k bodies, a step of 0.1 - 1.5 ms): the kernel's time is (units of the busiest CTA) x
 // (time per unit), and with only a few units per CTA the rounding of units / CTAs and the padding of the last
 // target tile are worth several per cent (N = 16 384, T6 x 256-body units: 704 units on 148 CTAs -> 5 where 4.76
 // are needed, and the 11th tile is 2/3 empty).  Pick the tile shape and unit size that minimise that product.
-int mid_variant(int n_targets, int n_sources)
+int mid_variant(int n_targets, int n_sources, int sms)
 {
     struct Cand { int id, T, UJ; };
     static const Cand cands[] = {{90, 6, 256}, {112, 6, 128}, {113, 6, 64}, {93, 8, 256}, {110, 8, 128}, {111, 8, 64}};
-    int dev = 0, sms = 148;
-    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (sms <= 0) {
+        int dev = 0;
+        sms = 148;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
     const long long src_pad = (long long)(n_sources + kSlotAlign - 1) / kSlotAlign * kSlotAlign;
     double best_cost = 1e300;
     int best = 90;
@@ -501,6 +513,18 @@ int nbody_autotune_report(char* buf, size_t buflen)
     std::lock_guard<std::mutex> lk(g_tune_mu);
     snprintf(buf, buflen, "%s", g_tune_report.c_str());
     return NBODY_OK;
+}
+
+int nbody_choose_variant(int n_targets, int n_sources, int sm_count, int* measured)
+{
+    if (n_targets <= 0 || n_sources < n_targets) {
+        fail(NBODY_E_INVALID, "need 0 < n_targets <= n_sources");
+        return 0;   // no variant has id 0
+    }
+    bool m = false;
+    const int id = static_variant(n_targets, n_sources, sm_count > 0 ? sm_count : 148, &m);
+    if (measured) *measured = m ? 1 : 0;
+    return id;
 }
 
 int nbody_variant_id(int index)

@@ -95,3 +95,24 @@ def test_ic_plummer_is_a_plummer_sphere(nb, oracle):
     ke, pe = oracle.energy(x, v, 1e-6)
     # virial equilibrium for the scheme's effective G = 1/2: 2*KE = -0.5*PE
     assert 0.8 < 2 * ke / (-0.5 * pe) < 1.2
+
+
+def test_kernel_choice_rules_are_host_logic(nb):
+    # NBODY_VARIANT_AUTO by size (DESIGN.md section 3 "Variant choice" / "Mid-size N"); host-only, no GPU involved
+    names = nb.variants()
+    pick = lambda t, s=None: nb.choose_variant(t, s or t)   # noqa: E731
+    assert names[pick(1024)[0]].startswith("S_TT2") and names[pick(8192)[0]].startswith("S_TT4")   # small-N family
+    assert pick(1024) == (85, False) and pick(3072) == (82, False) and pick(12287) == (82, False)
+    # mid sizes: tile shape x unit size by unit balance on 148 SMs (measured best in profiles/r1_small_family_sweep.jsonl
+    # and the runs recorded in DESIGN.md): N = 16 384 -> T8 x 128-body units, 32 768 -> T8 x 256, 50 000 -> T6 x 256
+    assert names[pick(16384)[0]].startswith("T8_NT256_UJ128") and names[pick(32768)[0]].startswith("T8_NT256_UJ256")
+    assert names[pick(50000)[0]].startswith("T6_NT256_UJ256")
+    assert all(not pick(n)[1] for n in (12288, 20000, 65535))
+    # large: one of the equivalent kernels, timed on the device
+    assert pick(65536)[1] and pick(1 << 20)[1] and pick(131072, 1 << 20)[1]
+    # a shard with few targets of many sources: more CTAs per SM instead of more targets per thread
+    assert names[pick(4096, 1 << 20)[0]].startswith("T2_NT256") and names[pick(1000, 1 << 20)[0]].startswith("T1_NT128")
+    with pytest.raises(nb.NBodyError):
+        nb.choose_variant(0, 10)
+    with pytest.raises(nb.NBodyError):
+        nb.choose_variant(20, 10)
