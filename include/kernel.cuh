@@ -49,4 +49,11 @@ void simulateHeadless_embParallel_fadl4(float4* d_bodies, float4* d_acceleration
  * its kernel; they affect the float4 overload above.  Defaults: EPS2, DT. */
 void simulate_set_parameters(float eps2, float dt);
 
+/* The reference runs on device 0 only (kernel.cu:630).  After simulate_set_devices(n) every device-pointer
+ * launcher above spreads its step over n GPUs of the box -- the current device, where the caller's arrays stay,
+ * plus the n-1 lowest-numbered others (NVLink peer access) -- so main.cpp's simulationLoopNoVisual scales with
+ * one added line and no other source change.  n <= 1 restores the single-device behaviour.  Throws
+ * std::runtime_error when n exceeds the devices present. */
+void simulate_set_devices(int n);
+
 #endif /* NBODY_KERNEL_CUH */

@@ -40,6 +40,18 @@ extern "C" {
 /* kernel variant: 0 = choose from N; others are listed by nbody_variant_info() */
 #define NBODY_VARIANT_AUTO 0
 
+/* position exchange of a multi-device context (nbody_params.n_devices > 1) */
+#define NBODY_EXCHANGE_P2P  0 /* fused: the step kernel's epilogue stores the new positions into every    */
+                              /* device's next source buffer (NVLink peer stores) and waits for its peers */
+                              /* on flags in peer memory; one launch per device per step, no library call */
+#define NBODY_EXCHANGE_NCCL 1 /* ncclAllGather of the packed positions on a second stream per device,     */
+                              /* overlapped with the own-slice interactions (libnccl.so.2 opened at run   */
+                              /* time; NBODY_E_STATE when it is not installed)                            */
+#define NBODY_EXCHANGE_P2P_EVENTS 2 /* the fused stores of P2P, the devices ordered by CUDA events between their  */
+                              /* streams instead of the in-kernel wait (what P2P itself falls back to for the   */
+                              /* small-N kernels); the only form that accepts one device listed more than once  */
+#define NBODY_MAX_DEVICES 16
+
 typedef struct nbody_ctx nbody_ctx;
 
 /* Runtime form of TestProject/constants.h:11-13,25-26 (compile-time macros in
@@ -57,6 +69,14 @@ typedef struct nbody_params {
     int   grid_ctas;     /* persistent CTAs to launch; 0 = SMs x occupancy   [0]              */
     double eps2_f64;     /* used when integrator == F64 (headless constants.h:14)  [0.002]    */
     double dt_f64;       /* used when integrator == F64 (headless constants.h:15)  [0.01]     */
+    int   deterministic; /* 1: no timing-based kernel choice (first of the family)    [0]     */
+                         /*    -- results are bit-identical either way, see nbody_autotune_report */
+    int   n_devices;     /* > 1: ONE context spanning devices[0..n_devices): device g owns    */
+                         /*    the g-th slice of the bodies; upload / step / download / energy */
+                         /*    / snapshot work on the whole system from one host thread.      */
+                         /*    Needs rank 0, world 1.  0 or 1: the single `device` above [0]  */
+    int   exchange;      /* NBODY_EXCHANGE_P2P | _NCCL | _P2P_EVENTS (n_devices > 1)  [P2P]   */
+    int   devices[NBODY_MAX_DEVICES];   /* CUDA ordinals, all different (see _P2P_EVENTS)     */
 } nbody_params;
 
 /* Fills *p with the defaults listed above (TestProject/constants.h). */
@@ -141,6 +161,15 @@ int nbody_shard_step_fused_async(nbody_ctx* ctx, void* stream);
  * progress for 20 s gives up; nbody_shard_barrier_timeouts() != 0 then means the state is invalid. */
 int nbody_shard_set_device_barrier(nbody_ctx* ctx, int enable);
 int nbody_shard_barrier_timeouts(nbody_ctx* ctx, int* timed_out);
+/* Time this GPU's step kernels stood in that flag wait since the last reset (measured by thread 0 of the
+ * kernel's first CTA with %globaltimer): total ns, longest single wait, number of waits.  Any pointer may be
+ * NULL; reset != 0 zeroes the counters afterwards.  On a multi-device context: the device with the largest total.
+ * This is where lock-step on the slowest GPU of a box shows up (the peers' stores themselves are 0.03 % of a step). */
+int nbody_shard_barrier_wait_ns(nbody_ctx* ctx, unsigned long long* total_ns, unsigned long long* max_ns,
+                                unsigned long long* waits, int reset);
+/* nbody_upload / nbody_snapshot_load on a context whose buffers peers are attached to rewrite BOTH source
+ * buffers: every rank must have finished its last step (and no rank may start the next) around that call --
+ * put a cross-rank barrier on each side.  A multi-device context (n_devices > 1) does this itself. */
 /* Geometry helper: bytes of one rank's padded slice for (N, world). */
 size_t nbody_shard_slot_bytes(int n_bodies, int world);
 
@@ -170,6 +199,14 @@ typedef struct nbody_step_opts {
 } nbody_step_opts;
 int nbody_step_opts_default(nbody_step_opts* o);
 int nbody_step_inplace_opts(float* d_bodies4, void* d_accel, void* d_vel, int n, const nbody_step_opts* o);
+
+/* Devices the in-place forms above (nbody_step_inplace_f4 / _opts, i.e. the reference's simulate()) spread a
+ * step over: the arrays stay where the caller put them (the current device, as kernel.cu:630 hard-codes device
+ * 0); device g of the list computes the g-th slice of the targets, reading X / V and writing X / V / A of that
+ * slice through NVLink peer access, against its own copy of the packed positions (one peer copy per step).
+ * So the reference's unmodified caller loop (main.cpp:142-160) scales over the GPUs of a box.  n <= 1 or
+ * devices == NULL: current device only (the default).  The first entry must be the device holding the arrays. */
+int nbody_set_devices(const int* devices, int n);
 
 /* Releases the per-(device, N) scratch the calls above keep between calls. */
 void nbody_release_cached(void);
@@ -228,6 +265,9 @@ int nbody_autotune_report(char* buf, size_t buflen);
 int nbody_choose_variant(int n_targets, int n_sources, int sm_count, int* measured);
 /* Variant / grid actually used by ctx (after AUTO resolution). */
 int nbody_ctx_info(nbody_ctx* ctx, int* variant, int* grid_ctas, int* ctas_per_sm, int* sm_count);
+/* Multi-device context: number of devices (1 for a plain context), NBODY_EXCHANGE_* in use, and whether
+ * the cross-device barrier lives in the step kernel (1) or is expressed with events between streams (0). */
+int nbody_group_info(nbody_ctx* ctx, int* n_devices, int* exchange, int* in_kernel_barrier);
 
 /* ---- initial conditions (host side; TestProject/utils.cpp:30-37) -------- */
 /* Reference distribution, seeded counter-based generator: positions

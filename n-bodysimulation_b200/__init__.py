@@ -18,7 +18,9 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libnbody_b200.so")
+# NBODY_LIB=libnbody_b200_sweep.so selects the sweep build (`make -C n-bodysimulation_b200 sweep`: every rejected
+# tile shape of round 1 as an extra variant) for tools/sweep.py; the default is the product library
+LIB_PATH = os.path.join(_HERE, os.environ.get("NBODY_LIB", "libnbody_b200.so"))
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(
@@ -28,6 +30,8 @@ if not os.path.exists(LIB_PATH):
 lib = C.CDLL(LIB_PATH)
 
 NBODY_INTEG_F32, NBODY_INTEG_F64, NBODY_INTEG_MIXED = 0, 1, 2
+NBODY_EXCHANGE_P2P, NBODY_EXCHANGE_NCCL, NBODY_EXCHANGE_P2P_EVENTS = 0, 1, 2
+NBODY_MAX_DEVICES = 16
 
 
 class NBodyParams(C.Structure):
@@ -35,7 +39,9 @@ class NBodyParams(C.Structure):
     _fields_ = [("n_bodies", C.c_int), ("rank", C.c_int), ("world", C.c_int),
                 ("eps2", C.c_float), ("dt", C.c_float), ("integrator", C.c_int),
                 ("device", C.c_int), ("variant", C.c_int), ("grid_ctas", C.c_int),
-                ("eps2_f64", C.c_double), ("dt_f64", C.c_double)]
+                ("eps2_f64", C.c_double), ("dt_f64", C.c_double),
+                ("deterministic", C.c_int), ("n_devices", C.c_int), ("exchange", C.c_int),
+                ("devices", C.c_int * NBODY_MAX_DEVICES)]
 
 
 class NBodyStepOpts(C.Structure):
@@ -76,6 +82,9 @@ SIGNATURES = {
     "nbody_shard_step_fused_async": (C.c_int, [_vp, _vp]),
     "nbody_shard_set_device_barrier": (C.c_int, [_vp, C.c_int]),
     "nbody_shard_barrier_timeouts": (C.c_int, [_vp, C.POINTER(C.c_int)]),
+    "nbody_shard_barrier_wait_ns": (C.c_int, [_vp, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong), C.c_int]),
+    "nbody_set_devices": (C.c_int, [C.POINTER(C.c_int), C.c_int]),
+    "nbody_group_info": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "nbody_step_inplace_f4": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_float, C.c_float]),
     "nbody_step_host_f3": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_double, C.c_double]),
     "nbody_step_opts_default": (C.c_int, [C.POINTER(NBodyStepOpts)]),
@@ -165,6 +174,16 @@ def simulate_set_parameters(eps2: float, dt: float) -> None:
     _eps2, _dt = float(eps2), float(dt)
 
 
+def set_devices(devices=None) -> None:
+    """nbody_set_devices: spread every following simulate() / simulate_opts() call over these GPUs (first = the
+    device holding the arrays); None or one device: single-device behaviour (the reference's, kernel.cu:630)"""
+    if not devices or len(devices) <= 1:
+        _check(lib.nbody_set_devices(None, 0))
+    else:
+        arr = (C.c_int * len(devices))(*devices)
+        _check(lib.nbody_set_devices(arr, len(devices)))
+
+
 def simulate(d_bodies, d_accelerations, d_velocity, N: int) -> None:
     """TestProject/kernel.cuh:2 -- DEVICE float4 arrays (torch CUDA tensors or raw
     pointers), one step in place, synchronous."""
@@ -242,12 +261,21 @@ class Simulation:
 
     def __init__(self, n: int, eps2: float = 0.002, dt: float = 0.1, *, rank: int = 0, world: int = 1,
                  device: int = 0, variant: int = 0, grid_ctas: int = 0, integrator: int = NBODY_INTEG_F32,
-                 eps2_f64: float = 0.002, dt_f64: float = 0.01):
+                 eps2_f64: float = 0.002, dt_f64: float = 0.01, devices=None, exchange: int = NBODY_EXCHANGE_P2P,
+                 deterministic: bool = False):
+        """devices=[d0, d1, ...]: ONE context spanning those GPUs (nbody_params.n_devices): the same upload / step /
+        download / energy / save calls then drive the whole box from this thread."""
         p = NBodyParams()
         _check(lib.nbody_params_default(C.byref(p)))
         p.n_bodies, p.rank, p.world, p.eps2, p.dt = n, rank, world, eps2, dt
         p.device, p.variant, p.grid_ctas, p.integrator = device, variant, grid_ctas, integrator
         p.eps2_f64, p.dt_f64 = eps2_f64, dt_f64
+        p.deterministic, p.exchange = int(deterministic), exchange
+        if devices is not None and len(devices) > 1:
+            assert len(devices) <= NBODY_MAX_DEVICES
+            p.n_devices = len(devices)
+            for i, d in enumerate(devices):
+                p.devices[i] = d
         self._h = _vp()
         _check(lib.nbody_create(C.byref(self._h), C.byref(p)))
         self.n = n
@@ -365,6 +393,17 @@ class Simulation:
         t = C.c_int()
         _check(lib.nbody_shard_barrier_timeouts(self._h, C.byref(t)))
         return t.value
+
+    def shard_barrier_wait_ns(self, reset: bool = False) -> dict:
+        """time this GPU's step kernels stood waiting for their peers' flags: total / longest / number of waits"""
+        t, m, w = C.c_ulonglong(), C.c_ulonglong(), C.c_ulonglong()
+        _check(lib.nbody_shard_barrier_wait_ns(self._h, C.byref(t), C.byref(m), C.byref(w), int(reset)))
+        return {"total_ns": t.value, "max_ns": m.value, "waits": w.value}
+
+    def group_info(self) -> dict:
+        n, e, b = C.c_int(), C.c_int(), C.c_int()
+        _check(lib.nbody_group_info(self._h, C.byref(n), C.byref(e), C.byref(b)))
+        return {"n_devices": n.value, "exchange": {NBODY_EXCHANGE_NCCL: "nccl", NBODY_EXCHANGE_P2P_EVENTS: "p2p-events"}.get(e.value, "p2p"), "in_kernel_barrier": bool(b.value)}
 
     def shard_step_fused_async(self, stream: int = 0) -> None:
         _check(lib.nbody_shard_step_fused_async(self._h, stream))

@@ -19,6 +19,25 @@ void simulate_set_parameters(float eps2, float dt)
     g_dt = dt;
 }
 
+// The reference's launcher asks for device 0 and nothing else (kernel.cu:630).  simulate_set_devices(n) spreads
+// every following simulate() / simulateHeadless*() call over n GPUs of the box: the current device (where the
+// caller's arrays live) plus the n-1 lowest-numbered others.  n <= 1: back to one device.
+void simulate_set_devices(int n)
+{
+    int cur = 0, ndev = 0;
+    if (cudaGetDevice(&cur) != cudaSuccess || cudaGetDeviceCount(&ndev) != cudaSuccess) throw std::runtime_error("simulate_set_devices: no CUDA device");
+    if (n > ndev) throw std::runtime_error("simulate_set_devices: " + std::to_string(n) + " devices asked for, " + std::to_string(ndev) + " present");
+    int list[NBODY_MAX_DEVICES];
+    int k = 0;
+    if (n > NBODY_MAX_DEVICES) n = NBODY_MAX_DEVICES;
+    if (n > 1) {
+        list[k++] = cur;
+        for (int d = 0; d < ndev && k < n; ++d)
+            if (d != cur) list[k++] = d;
+    }
+    if (nbody_set_devices(k > 1 ? list : nullptr, k) != NBODY_OK) throw std::runtime_error(std::string("simulate_set_devices: ") + nbody_last_error());
+}
+
 void simulate(float4* d_bodies, float4* d_accelerations, float4* d_velocity, int N)
 {
     const int rc = nbody_step_inplace_f4(reinterpret_cast<float*>(d_bodies), reinterpret_cast<float*>(d_accelerations),

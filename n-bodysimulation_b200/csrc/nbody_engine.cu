@@ -76,109 +76,82 @@ struct Variant {
 
 #define SVARIANT(id, TT, NT, UN) \
     { id, "S_TT" #TT "_NT" #NT "_U" #UN, TT, NT, 64, UN, 1, 1, 1, 0, small_kernel<TT, NT, UN>, 1 }
-// packed = FFMA2 path, 0 = scalar FFMA path (kept for the with/without evidence)
+// packed: 0 = scalar FFMA path (kept as the with/without evidence of the f32x2 choice), 1 = FADD2/FMUL2/FFMA2,
+// 5 / 6 / 7 / 8 = the same packed arithmetic in another source order (bit-identical results; ptxas' register
+// allocation differs by a few per cent, see tuned_large_variant).
+// The default table holds exactly what NBODY_VARIANT_AUTO can resolve to (static_variant, mid_variant, the tuner's
+// candidates) plus one scalar and one exemplar of each cluster mode.  The tile-shape sweep of round 1
+// (profiles/r1_variant_sweep_*.jsonl) is rebuilt with `make sweep` (-DNBODY_SWEEP_VARIANTS, libnbody_b200_sweep.so).
 const Variant kVariants[] = {
-    VARIANT(1, 4, 256, 256, 4, 1, 2),
-    VARIANT(2, 2, 256, 256, 4, 1, 4),
-    VARIANT(3, 2, 256, 256, 8, 1, 3),
-    VARIANT(4, 4, 128, 256, 4, 1, 4),
-    VARIANT(5, 8, 128, 256, 2, 1, 2),
-    VARIANT(6, 4, 256, 256, 8, 1, 2),
-    VARIANT(7, 4, 512, 256, 4, 1, 1),
-    VARIANT(8, 1, 256, 256, 8, 1, 6),
-    VARIANT(9, 4, 256, 256, 4, 0, 2),
-    VARIANT(10, 8, 256, 256, 2, 0, 1),
-    VARIANT(11, 2, 256, 256, 4, 0, 4),
-    VARIANT(12, 1, 128, 64, 8, 1, 8),
-    VARIANT(13, 2, 128, 128, 8, 1, 6),
-    VARIANT(14, 3, 256, 256, 4, 1, 2),
-    VARIANT(15, 6, 128, 256, 2, 1, 3),
-    VARIANT(16, 4, 256, 256, 4, 2, 2),
-    VARIANT(17, 4, 256, 256, 4, 3, 2),
-    VARIANT(18, 8, 128, 256, 2, 2, 2),
-    VARIANT(19, 8, 128, 256, 2, 3, 2),
-    VARIANT(20, 8, 128, 256, 4, 1, 2),
-    VARIANT(21, 8, 256, 256, 2, 1, 1),
-    VARIANT(22, 4, 192, 256, 4, 1, 3),
-    VARIANT(23, 4, 128, 256, 2, 1, 5),
-    VARIANT(24, 4, 256, 512, 4, 1, 2),
-    VARIANT(25, 4, 256, 1024, 4, 1, 2),
-    VARIANT(26, 6, 128, 256, 2, 1, 2),
-    VARIANT(27, 8, 128, 256, 1, 1, 2),
-    VARIANT(28, 8, 64, 256, 2, 1, 4),
-    VARIANT(29, 4, 320, 256, 4, 1, 2),
-    VARIANT(30, 8, 192, 256, 2, 1, 1),
-    VARIANT(31, 8, 256, 256, 1, 1, 2),
-    VARIANT(32, 8, 512, 256, 1, 1, 1),
-    VARIANT(33, 8, 512, 256, 2, 1, 1),
-    VARIANT(34, 6, 256, 256, 2, 1, 2),
-    VARIANT(35, 6, 512, 256, 2, 1, 1),
-    VARIANT(36, 5, 256, 256, 2, 1, 2),
-    VARIANT(37, 8, 256, 256, 4, 1, 1),
-    VARIANT(38, 8, 384, 256, 2, 1, 1),
-    VARIANT(39, 12, 128, 256, 1, 1, 2),
-    VARIANT(40, 12, 256, 256, 1, 1, 1),
-    VARIANT(41, 16, 128, 256, 1, 1, 2),
-    VARIANT(42, 16, 256, 256, 1, 1, 1),
-    VARIANT(43, 10, 256, 256, 1, 1, 1),
-    VARIANT(44, 8, 256, 512, 2, 1, 1),
+    VARIANT(3, 2, 256, 256, 8, 1, 3),        // few targets of many sources (a shard of a big system): 3 CTAs/SM
+    VARIANT(9, 4, 256, 256, 4, 0, 2),        // scalar FFMA exemplar
+    VARIANT(12, 1, 128, 64, 8, 1, 8),        // fewer than 2 048 targets of many sources
+    // large N, 256-body units (12 k .. 64 k sources): one arithmetic, four source orders
     VARIANT(45, 6, 256, 256, 2, 1, 1),
-    VARIANT(46, 6, 256, 256, 2, 4, 1),
-    VARIANT(47, 6, 256, 256, 4, 4, 1),
-    VARIANT(48, 6, 256, 256, 4, 1, 1),
-    VARIANT(49, 8, 256, 256, 2, 4, 1),
-    VARIANT(50, 6, 256, 512, 2, 4, 1),
-    VARIANT(51, 4, 256, 256, 4, 4, 2),
-    VARIANT(52, 6, 256, 256, 1, 4, 1),
-    VARIANT(53, 7, 256, 256, 2, 1, 1),
-    VARIANT(54, 4, 384, 256, 4, 1, 1),
-    VARIANT(55, 5, 384, 256, 2, 1, 1),
-    VARIANT(56, 6, 384, 256, 2, 1, 1),
-    VARIANT(57, 3, 512, 256, 4, 1, 1),
-    VARIANT(58, 4, 384, 256, 2, 1, 1),
     VARIANT(90, 6, 256, 256, 2, 5, 1),
-    VARIANT(91, 6, 256, 256, 2, 6, 1),
-    VARIANT(92, 8, 256, 256, 2, 5, 1),
-    VARIANT(93, 8, 256, 256, 2, 6, 1),
-    VARIANT(94, 7, 256, 256, 2, 6, 1),
-    VARIANT(95, 6, 256, 256, 4, 6, 1),
-    VARIANT(96, 8, 256, 512, 2, 6, 1),
     VARIANT(97, 6, 256, 256, 2, 7, 1),
     VARIANT(98, 6, 256, 256, 2, 8, 1),
-    VARIANT(99, 8, 256, 256, 2, 7, 1),
-    VARIANT(100, 8, 256, 512, 2, 8, 1),
+    // large N, 512-body units (>= 64 k sources): one arithmetic, three source orders
     VARIANT(101, 6, 256, 512, 2, 5, 1),
     VARIANT(102, 6, 256, 512, 2, 7, 1),
-    VARIANT(103, 6, 256, 1024, 2, 5, 1),
-    VARIANT(104, 6, 256, 1024, 2, 1, 1),
     VARIANT(105, 6, 256, 512, 2, 1, 1),
-    // finer source units for mid-size N (cost model in mid_variant): same kernels, 64- / 128-body units
+    // mid-size N (cost model in mid_variant): T8 tiles and 64- / 128-body units
+    VARIANT(93, 8, 256, 256, 2, 6, 1),
     VARIANT(110, 8, 256, 128, 2, 6, 1),
     VARIANT(111, 8, 256, 64, 2, 6, 1),
     VARIANT(112, 6, 256, 128, 2, 5, 1),
     VARIANT(113, 6, 256, 64, 2, 5, 1),
+    // thread-block-cluster exemplars (opt-in; measured neutral / slower, profiles/r1_ncu_cluster_evidence.md):
+    // m1 = TMA multicast of source units, m2 = j-split with DSMEM reduction
+    CVARIANT(60, 6, 256, 256, 2, 1, 1, 2, 1),
+    CVARIANT(64, 6, 256, 256, 2, 1, 1, 2, 2),
+    // small-N family: j-split inside the CTA, warp-shuffle reduction, no scratch
+    SVARIANT(82, 4, 128, 2),
+    SVARIANT(85, 2, 128, 4),
+#ifdef NBODY_SWEEP_VARIANTS
+    VARIANT(1, 4, 256, 256, 4, 1, 2),
+    VARIANT(2, 2, 256, 256, 4, 1, 4),
+    VARIANT(4, 4, 128, 256, 4, 1, 4),
+    VARIANT(5, 8, 128, 256, 2, 1, 2),
+    VARIANT(7, 4, 512, 256, 4, 1, 1),
+    VARIANT(8, 1, 256, 256, 8, 1, 6),
+    VARIANT(10, 8, 256, 256, 2, 0, 1),
+    VARIANT(11, 2, 256, 256, 4, 0, 4),
+    VARIANT(13, 2, 128, 128, 8, 1, 6),
+    VARIANT(14, 3, 256, 256, 4, 1, 2),
+    VARIANT(15, 6, 128, 256, 2, 1, 3),
+    VARIANT(21, 8, 256, 256, 2, 1, 1),
+    VARIANT(24, 4, 256, 512, 4, 1, 2),
+    VARIANT(25, 4, 256, 1024, 4, 1, 2),
+    VARIANT(34, 6, 256, 256, 2, 1, 2),
+    VARIANT(35, 6, 512, 256, 2, 1, 1),
+    VARIANT(36, 5, 256, 256, 2, 1, 2),
+    VARIANT(38, 8, 384, 256, 2, 1, 1),
+    VARIANT(40, 12, 256, 256, 1, 1, 1),
+    VARIANT(44, 8, 256, 512, 2, 1, 1),
+    VARIANT(48, 6, 256, 256, 4, 1, 1),
+    VARIANT(53, 7, 256, 256, 2, 1, 1),
+    VARIANT(55, 5, 384, 256, 2, 1, 1),
+    VARIANT(56, 6, 384, 256, 2, 1, 1),
+    VARIANT(91, 6, 256, 256, 2, 6, 1),
+    VARIANT(92, 8, 256, 256, 2, 5, 1),
+    VARIANT(96, 8, 256, 512, 2, 6, 1),
+    VARIANT(103, 6, 256, 1024, 2, 5, 1),
+    VARIANT(104, 6, 256, 1024, 2, 1, 1),
     VARIANT(114, 4, 256, 128, 4, 1, 2),
     VARIANT(115, 8, 256, 128, 2, 1, 1),
-    // thread-block-cluster variants: m1 = TMA multicast, m2 = j-split with DSMEM reduction
-    CVARIANT(60, 6, 256, 256, 2, 1, 1, 2, 1),
     CVARIANT(61, 6, 256, 256, 2, 1, 1, 4, 1),
     CVARIANT(62, 6, 256, 512, 2, 1, 1, 2, 1),
-    CVARIANT(63, 4, 256, 256, 4, 1, 2, 2, 1),
-    CVARIANT(64, 6, 256, 256, 2, 1, 1, 2, 2),
     CVARIANT(65, 6, 256, 256, 2, 1, 1, 4, 2),
     CVARIANT(66, 2, 256, 256, 8, 1, 3, 2, 2),
     CVARIANT(67, 2, 256, 256, 8, 1, 3, 4, 2),
-    CVARIANT(68, 1, 128, 64, 8, 1, 8, 4, 2),
-    CVARIANT(69, 2, 128, 128, 8, 1, 6, 8, 2),
     CVARIANT(70, 6, 256, 256, 2, 1, 1, 8, 2),
-    // small-N family: j-split inside the CTA, warp-shuffle reduction, no scratch
     SVARIANT(80, 8, 128, 2),
     SVARIANT(81, 8, 256, 2),
-    SVARIANT(82, 4, 128, 2),
     SVARIANT(83, 16, 256, 1),
     SVARIANT(84, 8, 64, 2),
-    SVARIANT(85, 2, 128, 4),
     SVARIANT(86, 8, 512, 1),
+#endif
 };
 const int kNumVariants = (int)(sizeof kVariants / sizeof kVariants[0]);
 constexpr size_t kFlagBytes = 4096;   // barrier flags behind packed[0]
@@ -191,7 +164,7 @@ const Variant* find_variant(int id)
     return nullptr;
 }
 
-int tuned_large_variant(int n_sources);
+int tuned_large_variant(int n_sources, bool deterministic);
 int mid_variant(int n_targets, int n_sources, int sms);
 
 // The static part of the choice (best of the r1 sweeps, profiles/r1_variant_sweep_*.jsonl; the cluster variants
@@ -205,16 +178,16 @@ int static_variant(int n_targets, int n_sources, int sms, bool* measured)
         return 82;                       // 4 targets / CTA
     }
     if (n_targets >= 12288 && n_sources < 65536) return mid_variant(n_targets, n_sources, sms);
-    if (n_targets >= 12288) { *measured = true; return 45; }
+    if (n_targets >= 12288) { *measured = true; return n_sources < 65536 ? 45 : 101; }
     if (n_targets >= 2048) return 3;     // T2 x 256 threads, 3 CTAs/SM
     return 12;                           // T1 x 128 threads, 64-body units
 }
 
-int auto_variant(int n_targets, int n_sources)
+int auto_variant(int n_targets, int n_sources, bool deterministic = false)
 {
     bool measured = false;
     const int id = static_variant(n_targets, n_sources, 0, &measured);
-    return measured ? tuned_large_variant(n_sources) : id;
+    return measured ? tuned_large_variant(n_sources, deterministic) : id;
 }
 
 // Mid-size N (12 k ... 64 k bodies, a step of 0.1 - 1.5 ms): the kernel's time is (units of the busiest CTA) x
@@ -245,6 +218,16 @@ int mid_variant(int n_targets, int n_sources, int sms)
 }
 
 int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+// The kernels take rsqrt.approx.ftz of (r^2 + eps2)^3: for the self term and the zero-mass padding r = 0, so a
+// subnormal eps2^3 is flushed to 0, rsqrt gives +inf and 0 * inf = NaN in every acceleration.  (The reference
+// divides by sqrtf of the subnormal, which is finite.)  Such softenings are rejected instead of answered wrongly.
+constexpr float kMinEps2 = 2.2737368e-13f;   // 2^-42: its cube 2^-126 is the smallest normal float
+bool eps2_representable(float eps2)
+{
+    const float e3 = (eps2 * eps2) * eps2;   // as the kernel forms it (two rounded multiplies)
+    return e3 >= 1.17549435e-38f;
+}
 
 // ---- launch plan for one (variant, targets, J) ---------------------------------------------------
 struct Plan {
@@ -296,9 +279,7 @@ int make_plan(const Variant* v, int sm_count, int grid_override, int n_targets, 
 
 int launch_force(const Variant* v, const Plan& pl, const ForceArgs& args_in, cudaStream_t st)
 {
-    ForceArgs args = args_in;
-    args.k_one = 1.0f;
-    args.k_negzero = -0.0f;
+    const ForceArgs& args = args_in;
     if (v->cs > 1) {
         cudaLaunchConfig_t cfg = {};
         cudaLaunchAttribute at[1];
@@ -326,27 +307,31 @@ int launch_pack(const float4* X, int n, float4* packed, int off, int n_cover, cu
 }
 
 // ---- which of the equivalent large-N kernels is fastest on this device ---------------------------------
-// The candidates below (T6 with 256- or 512-body units, one T8) issue the same instructions per interaction and
-// differ only in source order, i.e. in the register allocation ptxas happens to give them; measured, that is
-// worth +-3.5 % (register-bank conflicts on the 3-operand FFMA2; profiles/r1_variant_sweep_*).  Rather
-// than trust one allocation, the first large context of a process times each candidate for ~1 ms on
-// synthetic bodies and keeps the fastest (NBODY_LARGE_VARIANT=<id> in the environment overrides).
-const int kTuneCandidates[] = {45, 90, 96, 97, 98, 101, 102, 105};   // UJ 1024 (103, 104) is 0.3 % faster at N = 1 M but 4 % slower at the tuner's size: opt-in
-constexpr int kTuneBodies = 49152;   // whole tiles for T6 (1536) and T8 (2048): 0.9 ms per launch
+// The candidates of one family (T6 x 256 threads with 256-body units below 64 k sources, with 512-body units from
+// there on) issue the same instructions per interaction and form every sum in the same order: they differ only
+// in the order the source code names the targets / axes, i.e. in the register allocation ptxas happens to give
+// them; measured, that is worth +-3.5 % (register-bank conflicts on the 3-operand FFMA2; profiles/r1_variant_sweep_*).
+// Rather than trust one allocation, the first large context of a process times each candidate for ~1 ms on
+// synthetic bodies and keeps the fastest.  Because tile shape, unit size and grid are the same inside a family,
+// the RESULT does not depend on which one wins: bit-identical across processes, boxes and ranks
+// (tests/test_parity_gpu.py::test_tuner_candidates_are_bit_identical).  NBODY_LARGE_VARIANT=<id> in the
+// environment overrides; nbody_params.deterministic = 1 skips the timing and takes the first of the family.
+const int kTuneCandidates[] = {45, 90, 97, 98, 101, 102, 105};
+constexpr int kTuneBodies = 49152;   // whole T6 tiles (1536): 0.9 ms per launch
 std::mutex g_tune_mu;
 std::map<int, std::pair<int, int>> g_tuned;   // device -> (best with 256-body units, best overall)
 std::string g_tune_report;
 
-int tuned_large_variant(int n_sources)
+int tuned_large_variant(int n_sources, bool deterministic)
 {
     // 512-body units win at N >= 64 k (fewer barrier round trips) but cut a 16 k-body step into too few pieces
     const bool small_units = n_sources < 65536;
     int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return 45;
+    if (deterministic || cudaGetDevice(&dev) != cudaSuccess) return small_units ? 45 : 101;
     std::lock_guard<std::mutex> lk(g_tune_mu);
     auto it = g_tuned.find(dev);
     if (it != g_tuned.end()) return small_units ? it->second.first : it->second.second;
-    int best = 45, best256 = 45;
+    int best = 101, best256 = 45;
     if (const char* env = getenv("NBODY_LARGE_VARIANT")) {
         const int id = atoi(env);
         if (find_variant(id) && !find_variant(id)->small) { g_tuned[dev] = std::make_pair(id, id); g_tune_report = "forced by NBODY_LARGE_VARIANT"; return id; }
@@ -392,7 +377,7 @@ int tuned_large_variant(int n_sources)
         }
         snprintf(line, sizeof line, "%s%d:%.3fms", g_tune_report.empty() ? "" : " ", id, ms);
         g_tune_report += line;
-        if (ms < best_ms) { best_ms = ms; best = id; }
+        if (v->UJ == 512 && ms < best_ms) { best_ms = ms; best = id; }
         if (v->UJ == 256 && ms < best256_ms) { best256_ms = ms; best256 = id; }
     }
     cudaGetLastError();
@@ -419,7 +404,7 @@ struct nbody_ctx {
     float4* partial = nullptr;
     unsigned* counters = nullptr;
     double* energy_part = nullptr;
-    unsigned long long* clk = nullptr;          // {clock64, globaltimer} x {entry, exit} of CTA 0 of the last force kernel
+    unsigned long long* clk = nullptr;          // [0..3] {clock64, globaltimer} x {entry, exit} of CTA 0 of the last force kernel; [4..6] flag-wait ns: sum, max, count
     float4* stage = nullptr;                     // upload staging, float4[n]
     Plan plan_full, plan_local, plan_remote;
     cudaStream_t stream = nullptr;
@@ -442,9 +427,16 @@ struct nbody_ctx {
     bool device_barrier = false;
     unsigned long long fused_steps = 0;
     unsigned* bar_done = nullptr;                // 256 B: [0] CTA arrival counter, [16] time-out mark
+    // multi-device context (nbody_params.n_devices > 1, nbody_group.inl): this object only holds the per-device
+    // sharded contexts and what orders them; every other member above stays empty
+    std::vector<nbody_ctx*> kids;
+    struct Group* group = nullptr;
 };
 
 namespace {
+
+int group_create(nbody_ctx** out, const nbody_params* p);   // nbody_group.inl
+void group_destroy(nbody_ctx* c);
 
 int per_rank(int n, int world) { return round_up((n + world - 1) / world, 2); }
 
@@ -468,6 +460,45 @@ int set_device(nbody_ctx* c)
 {
     CU(cudaSetDevice(c->p.device));
     return NBODY_OK;
+}
+
+// launch plans of c->var for this context's geometry + the split-tile scratch they need
+int plan_scratch(nbody_ctx* c)
+{
+    const int UJ = c->var->UJ;
+    const int units_total = c->n_src_pad / UJ, units_own = c->slot_bodies / UJ;
+    int rc = make_plan(c->var, c->sm_count, c->p.grid_ctas, c->n_targets, units_total, &c->plan_full);
+    if (rc) return rc;
+    size_t partial_bytes = c->plan_full.partial_bytes;
+    if (c->p.world > 1) {
+        rc = make_plan(c->var, c->sm_count, c->p.grid_ctas, c->n_targets, units_own, &c->plan_local);
+        if (rc) return rc;
+        rc = make_plan(c->var, c->sm_count, c->p.grid_ctas, c->n_targets, units_total - units_own, &c->plan_remote);
+        if (rc) return rc;
+        if (c->plan_local.partial_bytes > partial_bytes) partial_bytes = c->plan_local.partial_bytes;
+        if (c->plan_remote.partial_bytes > partial_bytes) partial_bytes = c->plan_remote.partial_bytes;
+    }
+    cudaFree(c->partial); cudaFree(c->counters);
+    c->partial = nullptr; c->counters = nullptr;
+    CU(cudaMalloc(&c->partial, partial_bytes));
+    CU(cudaMalloc(&c->counters, (size_t)c->plan_full.num_counters * sizeof(unsigned)));
+    CU(cudaMemset(c->counters, 0, (size_t)c->plan_full.num_counters * sizeof(unsigned)));
+    return NBODY_OK;
+}
+
+// run another kernel variant from now on (nbody_snapshot_load re-pins the saver's)
+int repin_variant(nbody_ctx* c, const Variant* v)
+{
+    int rc = set_device(c);
+    if (rc) return rc;
+    CU(cudaStreamSynchronize(c->stream));
+    if (c->step_graph) { cudaGraphExecDestroy(c->step_graph); c->step_graph = nullptr; }
+    c->graph_failed = false;
+    const Variant* old = c->var;
+    c->var = v;
+    rc = plan_scratch(c);
+    if (rc) { c->var = old; plan_scratch(c); }
+    return rc;
 }
 
 }  // namespace
@@ -501,7 +532,7 @@ int nbody_variant_info(int id, char* buf, size_t buflen)
         if (v->small) snprintf(cl, sizeof cl, ", small-N family: %d targets/CTA, sources split over the CTA, warp-shuffle reduction", v->T);
         snprintf(buf, buflen, "%s: %d targets/thread, %d threads/CTA, %d sources/tile, unroll %d pairs, %s FP32, min %d CTAs/SM, %zu B smem%s",
                  v->name, v->T, v->NT, v->UJ, v->unroll,
-                 v->packed == 0 ? "scalar" : v->packed == 1 ? "packed f32x2" : v->packed == 2 ? "packed f32x2 (all FFMA2)" : v->packed == 3 ? "packed f32x2 + prefetch" : v->packed == 4 ? "packed f32x2 + first-pair prefetch" : v->packed == 5 ? "packed f32x2, targets reversed" : v->packed == 6 ? "packed f32x2, target-outer order" : "packed f32x2, z-first order",
+                 v->packed == 0 ? "scalar" : v->packed == 1 ? "packed f32x2" : v->packed == 5 ? "packed f32x2, targets reversed" : v->packed == 6 ? "packed f32x2, target-outer order" : "packed f32x2, z-first order",
                  v->minb, v->smem(), cl);
     }
     return kNumVariants;
@@ -541,6 +572,7 @@ size_t nbody_shard_slot_bytes(int n_bodies, int world)
 void nbody_destroy(nbody_ctx* c)
 {
     if (!c) return;
+    if (c->group || !c->kids.empty()) { group_destroy(c); return; }
     cudaSetDevice(c->p.device);
     for (int r = 0; r <= kMaxPeers; ++r)
         if (c->peer_ipc[r]) { cudaIpcCloseMemHandle(c->peer_packed[r][0]); cudaIpcCloseMemHandle(c->peer_packed[r][1]); }
@@ -566,6 +598,9 @@ int nbody_create(nbody_ctx** out, const nbody_params* p)
     // the self term is 0 * m / eps2^1.5 and the zero-mass padding sits at the
     // origin: both need eps2 > 0 to stay finite
     if (!((f64 ? p->eps2_f64 : (double)p->eps2) > 0.0)) return fail(NBODY_E_INVALID, "eps2 must be > 0");
+    if (!eps2_representable(f64 ? (float)p->eps2_f64 : p->eps2))
+        return fail(NBODY_E_INVALID, "eps2 = %g is too small: eps2^3 must be a normal float (eps2 >= %g), or the self term 0 * rsqrt(eps2^3) is NaN", f64 ? p->eps2_f64 : (double)p->eps2, (double)kMinEps2);
+    if (p->n_devices > 1) return group_create(out, p);
     int ndev = 0;
     CU(cudaGetDeviceCount(&ndev));
     if (p->device < 0 || p->device >= ndev) return fail(NBODY_E_INVALID, "device %d not present (%d devices)", p->device, ndev);
@@ -588,22 +623,13 @@ int nbody_create(nbody_ctx** out, const nbody_params* p)
     c->slot_bodies = round_up(c->per, kSlotAlign);
     c->n_src_pad = c->slot_bodies * p->world;
 
-    const int vid = p->variant == NBODY_VARIANT_AUTO ? auto_variant(c->n_targets, c->n) : p->variant;
+    const int vid = p->variant == NBODY_VARIANT_AUTO ? auto_variant(c->n_targets, c->n, p->deterministic != 0) : p->variant;
     c->var = find_variant(vid);
     if (!c->var) { delete c; return fail(NBODY_E_INVALID, "unknown kernel variant %d", vid); }
 
-    const int UJ = c->var->UJ;
-    const int units_total = c->n_src_pad / UJ, units_own = c->slot_bodies / UJ;
 #define TRY(x) do { rc = (x); if (rc) { nbody_destroy(c); return rc; } } while (0)
 #define TRYCU(x) do { cudaError_t e2 = (x); if (e2 != cudaSuccess) { nbody_destroy(c); return fail(NBODY_E_CUDA, "%s: %s", #x, cudaGetErrorString(e2)); } } while (0)
-    TRY(make_plan(c->var, c->sm_count, p->grid_ctas, c->n_targets, units_total, &c->plan_full));
-    size_t partial_bytes = c->plan_full.partial_bytes;
-    if (p->world > 1) {
-        TRY(make_plan(c->var, c->sm_count, p->grid_ctas, c->n_targets, units_own, &c->plan_local));
-        TRY(make_plan(c->var, c->sm_count, p->grid_ctas, c->n_targets, units_total - units_own, &c->plan_remote));
-        if (c->plan_local.partial_bytes > partial_bytes) partial_bytes = c->plan_local.partial_bytes;
-        if (c->plan_remote.partial_bytes > partial_bytes) partial_bytes = c->plan_remote.partial_bytes;
-    }
+    TRY(plan_scratch(c));
     const size_t tb = (size_t)c->n_targets * sizeof(float4);
     const size_t sb = (size_t)c->n_src_pad * sizeof(float4);
     TRYCU(cudaMalloc(&c->X, tb));
@@ -616,15 +642,12 @@ int nbody_create(nbody_ctx** out, const nbody_params* p)
     TRYCU(cudaMalloc(&c->bar_done, 256));
     TRYCU(cudaMemset(c->bar_done, 0, 256));
     TRYCU(cudaMalloc(&c->packed[1], sb));
-    TRYCU(cudaMalloc(&c->partial, partial_bytes));
-    TRYCU(cudaMalloc(&c->clk, 4 * sizeof(unsigned long long)));
-    TRYCU(cudaMemset(c->clk, 0, 4 * sizeof(unsigned long long)));
-    TRYCU(cudaMalloc(&c->counters, (size_t)c->plan_full.num_counters * sizeof(unsigned)));
+    TRYCU(cudaMalloc(&c->clk, 8 * sizeof(unsigned long long)));
+    TRYCU(cudaMemset(c->clk, 0, 8 * sizeof(unsigned long long)));
     TRYCU(cudaMemset(c->V, 0, tb));
     TRYCU(cudaMemset(c->A, 0, tb));
     TRYCU(cudaMemset(c->packed[0], 0, sb));
     TRYCU(cudaMemset(c->packed[1], 0, sb));
-    TRYCU(cudaMemset(c->counters, 0, (size_t)c->plan_full.num_counters * sizeof(unsigned)));
     TRYCU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     TRYCU(cudaEventCreate(&c->ev0));
     TRYCU(cudaEventCreate(&c->ev1));
@@ -638,6 +661,7 @@ int nbody_create(nbody_ctx** out, const nbody_params* p)
 int nbody_ctx_info(nbody_ctx* c, int* variant, int* grid_ctas, int* ctas_per_sm, int* sm_count)
 {
     if (!c) return fail(NBODY_E_INVALID, "null context");
+    if (!c->kids.empty()) c = c->kids[0];   // every device of a multi-device context runs the same plan
     if (variant) *variant = c->var->id;
     if (grid_ctas) *grid_ctas = c->plan_full.grid;
     if (ctas_per_sm) *ctas_per_sm = c->plan_full.occ;
@@ -648,6 +672,11 @@ int nbody_ctx_info(nbody_ctx* c, int* variant, int* grid_ctas, int* ctas_per_sm,
 int nbody_owned_range(nbody_ctx* c, int* begin, int* count)
 {
     if (!c) return fail(NBODY_E_INVALID, "null context");
+    if (!c->kids.empty()) {   // the whole system
+        if (begin) *begin = 0;
+        if (count) *count = c->n;
+        return NBODY_OK;
+    }
     if (begin) *begin = c->t_begin;
     if (count) *count = c->n_targets;
     return NBODY_OK;
@@ -658,3 +687,4 @@ int nbody_owned_range(nbody_ctx* c, int* begin, int* count)
 #include "nbody_engine_api.inl"
 #include "nbody_render.inl"
 #include "nbody_records.inl"
+#include "nbody_group.inl"

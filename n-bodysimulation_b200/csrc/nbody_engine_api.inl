@@ -3,6 +3,18 @@
 
 namespace {
 
+// multi-device contexts (nbody_group.inl)
+int group_upload(nbody_ctx* c, const float* x4, const float* v4);
+int group_download(nbody_ctx* c, float* x4, float* v4, float* a4);
+int group_step_async(nbody_ctx* c, int nsteps);
+int group_sync(nbody_ctx* c);
+int group_elapsed_ms(nbody_ctx* c, float* ms);
+int group_energy(nbody_ctx* c, double* ke, double* pe);
+int group_barrier_timeouts(nbody_ctx* c, int* timed_out);
+int group_barrier_wait_ns(nbody_ctx* c, unsigned long long* total_ns, unsigned long long* max_ns, unsigned long long* waits, int reset);
+inline bool is_group(const nbody_ctx* c) { return !c->kids.empty(); }
+#define NOT_FOR_GROUP(c) do { if (is_group(c)) return fail(NBODY_E_STATE, "%s: not valid on a multi-device context (it drives its own shards)", __func__); } while (0)
+
 // one unsharded step: all sources, fused integrate, new positions into the other buffer
 int enqueue_full_step(nbody_ctx* c, cudaStream_t st)
 {
@@ -50,14 +62,10 @@ bool ensure_step_graph(nbody_ctx* c)
     return false;
 }
 
-}  // namespace
-
-extern "C" {
-
-int nbody_upload(nbody_ctx* c, const float* x4, const float* v4)
+// host -> device of one context, enqueued on its stream (nbody_upload synchronises; a multi-device
+// context enqueues on every device first, so the copies of the G devices overlap)
+int upload_enqueue(nbody_ctx* c, const float* x4, const float* v4)
 {
-    TRACE_CALL();
-    if (!c || !x4) return fail(NBODY_E_INVALID, "null argument");
     int rc = set_device(c);
     if (rc) return rc;
     // stage all N positions once, pack each rank's slice into its padded slot
@@ -78,9 +86,55 @@ int nbody_upload(nbody_ctx* c, const float* x4, const float* v4)
         if (v4) e = cudaMemcpyAsync(c->V, v4 + 4 * (size_t)c->t_begin, (size_t)c->n_targets * sizeof(float4), cudaMemcpyHostToDevice, c->stream);
         else e = cudaMemsetAsync(c->V, 0, (size_t)c->n_targets * sizeof(float4), c->stream);
     }
-    if (e == cudaSuccess && rc == 0) e = cudaStreamSynchronize(c->stream);
     if (rc) return rc;
     if (e != cudaSuccess) return fail(NBODY_E_CUDA, "upload failed: %s", cudaGetErrorString(e));
+    return NBODY_OK;
+}
+
+// kinetic energy and pair potential of n bodies in device arrays X, V on c's device and stream
+int energy_of(nbody_ctx* c, const float4* X, const float4* V, int n, double eps2, double* ke, double* pe)
+{
+    int rc = set_device(c);
+    if (rc) return rc;
+    const int blocks = (n + 255) / 256;
+    if (!c->energy_part) CU(cudaMalloc(&c->energy_part, (size_t)blocks * 2 * sizeof(double)));
+    energy_kernel<<<blocks, 256, 0, c->stream>>>(X, V, n, eps2, c->energy_part);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CU(cudaGetLastError());
+    std::vector<double> h((size_t)blocks * 2);
+    CU(cudaMemcpyAsync(h.data(), c->energy_part, h.size() * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    double k = 0.0, p = 0.0;
+    for (int b = 0; b < blocks; ++b) { k += h[2 * b]; p += h[2 * b + 1]; }
+    *ke = k;
+    *pe = 0.5 * p;   // ordered pairs -> i<j
+    return NBODY_OK;
+}
+
+// device -> host of the owned bodies, enqueued on the context's stream (ordered after its steps)
+int download_enqueue(nbody_ctx* c, float* x4, float* v4, float* a4)
+{
+    int rc = set_device(c);
+    if (rc) return rc;
+    const size_t tb = (size_t)c->n_targets * sizeof(float4);
+    if (x4) CU(cudaMemcpyAsync(x4, c->X, tb, cudaMemcpyDeviceToHost, c->stream));
+    if (v4) CU(cudaMemcpyAsync(v4, c->V, tb, cudaMemcpyDeviceToHost, c->stream));
+    if (a4) CU(cudaMemcpyAsync(a4, c->A, tb, cudaMemcpyDeviceToHost, c->stream));
+    return NBODY_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int nbody_upload(nbody_ctx* c, const float* x4, const float* v4)
+{
+    TRACE_CALL();
+    if (!c || !x4) return fail(NBODY_E_INVALID, "null argument");
+    if (is_group(c)) return group_upload(c, x4, v4);
+    int rc = upload_enqueue(c, x4, v4);
+    if (rc) return rc;
+    CU(cudaStreamSynchronize(c->stream));
     return NBODY_OK;
 }
 
@@ -88,13 +142,10 @@ int nbody_download(nbody_ctx* c, float* x4, float* v4, float* a4)
 {
     TRACE_CALL();
     if (!c) return fail(NBODY_E_INVALID, "null context");
-    int rc = set_device(c);
+    if (is_group(c)) return group_download(c, x4, v4, a4);
+    int rc = download_enqueue(c, x4, v4, a4);
     if (rc) return rc;
-    const size_t tb = (size_t)c->n_targets * sizeof(float4);
     CU(cudaStreamSynchronize(c->stream));
-    if (x4) CU(cudaMemcpy(x4, c->X, tb, cudaMemcpyDeviceToHost));
-    if (v4) CU(cudaMemcpy(v4, c->V, tb, cudaMemcpyDeviceToHost));
-    if (a4) CU(cudaMemcpy(a4, c->A, tb, cudaMemcpyDeviceToHost));
     return NBODY_OK;
 }
 
@@ -103,6 +154,7 @@ int nbody_step_async(nbody_ctx* c, int nsteps)
     TRACE_CALL();
     if (!c) return fail(NBODY_E_INVALID, "null context");
     if (nsteps < 0) return fail(NBODY_E_INVALID, "nsteps must be >= 0");
+    if (is_group(c)) return group_step_async(c, nsteps);
     if (c->p.world != 1) return fail(NBODY_E_STATE, "nbody_step on a sharded context; use nbody_shard_*");
     int rc = set_device(c);
     if (rc) return rc;
@@ -135,6 +187,7 @@ int nbody_sync(nbody_ctx* c)
 {
     TRACE_CALL();
     if (!c) return fail(NBODY_E_INVALID, "null context");
+    if (is_group(c)) return group_sync(c);
     int rc = set_device(c);
     if (rc) return rc;
     CU(cudaStreamSynchronize(c->stream));
@@ -151,6 +204,7 @@ int nbody_step(nbody_ctx* c, int nsteps)
 int nbody_elapsed_ms(nbody_ctx* c, float* ms)
 {
     if (!c || !ms) return fail(NBODY_E_INVALID, "null argument");
+    if (is_group(c)) return group_elapsed_ms(c, ms);
     if (!c->timed) return fail(NBODY_E_STATE, "no timed call yet");
     CU(cudaEventSynchronize(c->ev1));
     CU(cudaEventElapsedTime(ms, c->ev0, c->ev1));
@@ -160,6 +214,7 @@ int nbody_elapsed_ms(nbody_ctx* c, float* ms)
 int nbody_kernel_clock_mhz(nbody_ctx* c, float* mhz)
 {
     if (!c || !mhz) return fail(NBODY_E_INVALID, "null argument");
+    if (is_group(c)) c = c->kids[0];
     int rc = set_device(c);
     if (rc) return rc;
     unsigned long long h[4];
@@ -174,29 +229,17 @@ int nbody_energy(nbody_ctx* c, double* ke, double* pe)
 {
     TRACE_CALL();
     if (!c || !ke || !pe) return fail(NBODY_E_INVALID, "null argument");
+    if (is_group(c)) return group_energy(c, ke, pe);
     if (c->p.world != 1) return fail(NBODY_E_STATE, "nbody_energy needs an unsharded context");
-    int rc = set_device(c);
-    if (rc) return rc;
-    const int blocks = (c->n + 255) / 256;
-    if (!c->energy_part) CU(cudaMalloc(&c->energy_part, (size_t)blocks * 2 * sizeof(double)));
     const double eps2 = c->p.integrator == NBODY_INTEG_F64 ? c->p.eps2_f64 : (double)c->p.eps2;
-    energy_kernel<<<blocks, 256, 0, c->stream>>>(c->X, c->V, c->n, eps2, c->energy_part);
-    g_launches.fetch_add(1, std::memory_order_relaxed);
-    CU(cudaGetLastError());
-    std::vector<double> h((size_t)blocks * 2);
-    CU(cudaMemcpyAsync(h.data(), c->energy_part, h.size() * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaStreamSynchronize(c->stream));
-    double k = 0.0, p = 0.0;
-    for (int b = 0; b < blocks; ++b) { k += h[2 * b]; p += h[2 * b + 1]; }
-    *ke = k;
-    *pe = 0.5 * p;   // ordered pairs -> i<j
-    return NBODY_OK;
+    return energy_of(c, c->X, c->V, c->n, eps2, ke, pe);
 }
 
 // ---- sharded stepping ---------------------------------------------------------------------------------
 int nbody_shard_sources(nbody_ctx* c, int which, void** dptr, size_t* total_bytes, size_t* slot_bytes)
 {
     if (!c || (which != 0 && which != 1)) return fail(NBODY_E_INVALID, "bad argument");
+    NOT_FOR_GROUP(c);
     if (dptr) *dptr = c->packed[c->cur ^ which];
     if (total_bytes) *total_bytes = (size_t)c->n_src_pad * sizeof(float4);
     if (slot_bytes) *slot_bytes = (size_t)c->slot_bodies * sizeof(float4);
@@ -207,6 +250,7 @@ int nbody_shard_local_async(nbody_ctx* c, void* stream)
 {
     TRACE_CALL();
     if (!c) return fail(NBODY_E_INVALID, "null context");
+    NOT_FOR_GROUP(c);
     int rc = set_device(c);
     if (rc) return rc;
     cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
@@ -223,6 +267,7 @@ int nbody_shard_remote_async(nbody_ctx* c, void* stream)
 {
     TRACE_CALL();
     if (!c) return fail(NBODY_E_INVALID, "null context");
+    NOT_FOR_GROUP(c);
     int rc = set_device(c);
     if (rc) return rc;
     if (c->p.world == 1) return NBODY_OK;
@@ -246,6 +291,7 @@ int nbody_shard_remote_async(nbody_ctx* c, void* stream)
 int nbody_shard_ipc_handles(nbody_ctx* c, void* handles128)
 {
     if (!c || !handles128) return fail(NBODY_E_INVALID, "null argument");
+    NOT_FOR_GROUP(c);
     int rc = set_device(c);
     if (rc) return rc;
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handles are 64 bytes");
@@ -259,6 +305,7 @@ int nbody_shard_ipc_handles(nbody_ctx* c, void* handles128)
 static int attach_checks(nbody_ctx* c, int peer)
 {
     if (!c) return fail(NBODY_E_INVALID, "null context");
+    NOT_FOR_GROUP(c);
     if (c->p.world < 2) return fail(NBODY_E_STATE, "an unsharded context has no peers");
     if (c->p.world > kMaxPeers + 1) return fail(NBODY_E_STATE, "fused exchange supports up to %d ranks", kMaxPeers + 1);
     if (peer < 0 || peer >= c->p.world || peer == c->p.rank) return fail(NBODY_E_INVALID, "bad peer rank %d (this is rank %d of %d)", peer, c->p.rank, c->p.world);
@@ -306,6 +353,7 @@ int nbody_shard_attach_ptr(nbody_ctx* c, int peer, void* buf0, void* buf1)
 int nbody_shard_buffers(nbody_ctx* c, void** buf0, void** buf1)
 {
     if (!c || !buf0 || !buf1) return fail(NBODY_E_INVALID, "null argument");
+    NOT_FOR_GROUP(c);
     *buf0 = c->packed[0]; *buf1 = c->packed[1];
     return NBODY_OK;
 }
@@ -314,6 +362,7 @@ int nbody_shard_step_fused_async(nbody_ctx* c, void* stream)
 {
     TRACE_CALL();
     if (!c) return fail(NBODY_E_INVALID, "null context");
+    NOT_FOR_GROUP(c);
     int rc = set_device(c);
     if (rc) return rc;
     cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
@@ -348,6 +397,7 @@ int nbody_shard_step_fused_async(nbody_ctx* c, void* stream)
 int nbody_shard_set_device_barrier(nbody_ctx* c, int enable)
 {
     if (!c) return fail(NBODY_E_INVALID, "null context");
+    NOT_FOR_GROUP(c);
     if (enable && c->p.world > 1 && c->var->small)
         return fail(NBODY_E_STATE, "variant %s (small-N family) has no in-kernel barrier; synchronise the ranks from the caller", c->var->name);
     if (c->fused_steps != 0 && (enable != 0) != c->device_barrier)
@@ -359,9 +409,26 @@ int nbody_shard_set_device_barrier(nbody_ctx* c, int enable)
 int nbody_shard_barrier_timeouts(nbody_ctx* c, int* timed_out)
 {
     if (!c || !timed_out) return fail(NBODY_E_INVALID, "null argument");
+    if (is_group(c)) return group_barrier_timeouts(c, timed_out);
     int rc = set_device(c);
     if (rc) return rc;
     CU(cudaMemcpy(timed_out, reinterpret_cast<int*>(c->bar_done) + 16, sizeof(int), cudaMemcpyDeviceToHost));
+    return NBODY_OK;
+}
+
+int nbody_shard_barrier_wait_ns(nbody_ctx* c, unsigned long long* total_ns, unsigned long long* max_ns, unsigned long long* waits, int reset)
+{
+    if (!c) return fail(NBODY_E_INVALID, "null context");
+    if (is_group(c)) return group_barrier_wait_ns(c, total_ns, max_ns, waits, reset);
+    int rc = set_device(c);
+    if (rc) return rc;
+    unsigned long long h[3] = {0, 0, 0};
+    CU(cudaDeviceSynchronize());   // the steps may run on a caller's stream: wait for all of this device
+    CU(cudaMemcpy(h, c->clk + 4, sizeof h, cudaMemcpyDeviceToHost));
+    if (total_ns) *total_ns = h[0];
+    if (max_ns) *max_ns = h[1];
+    if (waits) *waits = h[2];
+    if (reset) CU(cudaMemset(c->clk + 4, 0, sizeof h));
     return NBODY_OK;
 }
 
@@ -433,6 +500,156 @@ int one_step_on_device(Cached* k, float4* dX, float4* dA, float4* dV, int n, flo
     return launch_force(k->var, k->plan, a, 0);
 }
 
+// ---- the in-place step spread over several GPUs (nbody_set_devices) --------------------------------------
+// The caller's arrays stay on the first device (the reference's launcher knows only device 0, kernel.cu:630).
+// Device g computes the g-th slice of the targets: its kernel reads X / V and writes X / V / A of that slice
+// straight in the first device's memory (NVLink peer loads / stores, 80 B per body and step) and streams the
+// sources from its own copy of the packed snapshot (one peer copy of 16 N bytes per step).
+struct MultiDev {
+    int device = 0, t_begin = 0, n_targets = 0;
+    Plan plan;
+    float4 *packed = nullptr, *partial = nullptr;
+    unsigned* counters = nullptr;
+    cudaStream_t st = nullptr;   // null on the first device: it works on the caller's (legacy default) stream
+};
+struct CachedMulti {
+    const Variant* var = nullptr;
+    int n_pad = 0;
+    cudaEvent_t packed_ready = nullptr;
+    std::vector<MultiDev> d;
+};
+std::vector<int> g_inplace_devices;                                           // guarded by g_cache_mu
+std::map<std::pair<std::vector<int>, std::pair<int, int>>, CachedMulti> g_cache_multi;   // (devices, (N, variant))
+
+void free_cached_multi(CachedMulti& k)
+{
+    for (MultiDev& m : k.d) {
+        cudaSetDevice(m.device);
+        cudaFree(m.packed); cudaFree(m.partial); cudaFree(m.counters);
+        if (m.st) cudaStreamDestroy(m.st);
+    }
+    if (!k.d.empty()) { cudaSetDevice(k.d[0].device); if (k.packed_ready) cudaEventDestroy(k.packed_ready); }
+    k = CachedMulti();
+}
+
+int get_cached_multi(int n, int variant, CachedMulti** out)
+{
+    const std::vector<int>& devs = g_inplace_devices;
+    const int G = (int)devs.size();
+    int dev0 = 0;
+    CU(cudaGetDevice(&dev0));
+    if (dev0 != devs[0]) return fail(NBODY_E_STATE, "nbody_set_devices: the first device of the list (%d) must be the current one (%d), where the arrays live", devs[0], dev0);
+    CachedMulti& k = g_cache_multi[std::make_pair(devs, std::make_pair(n, variant))];
+    if (k.var) { *out = &k; return NBODY_OK; }
+    const int per = per_rank(n, G);
+    if ((long long)per * (G - 1) >= n) { g_cache_multi.erase(std::make_pair(devs, std::make_pair(n, variant))); return fail(NBODY_E_INVALID, "N=%d is too small to spread over %d devices", n, G); }
+    const Variant* var = find_variant(variant == NBODY_VARIANT_AUTO ? auto_variant(per, n) : variant);
+    if (!var) { g_cache_multi.erase(std::make_pair(devs, std::make_pair(n, variant))); return fail(NBODY_E_INVALID, "unknown kernel variant %d", variant); }
+    k.n_pad = round_up(n, kSlotAlign);
+    k.d.assign(G, MultiDev());
+    int rc = NBODY_OK;
+    cudaError_t e = cudaSuccess;
+    for (int g = 0; g < G && !rc && e == cudaSuccess; ++g) {
+        MultiDev& m = k.d[g];
+        m.device = devs[g];
+        m.t_begin = g * per;
+        m.n_targets = n - m.t_begin < per ? n - m.t_begin : per;
+        e = cudaSetDevice(m.device);
+        cudaDeviceProp prop;
+        if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, m.device);
+        if (e != cudaSuccess) break;
+        if (prop.major < 10) { rc = fail(NBODY_E_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", m.device, prop.major, prop.minor); break; }
+        if (g > 0) {   // its kernel works on the first device's arrays
+            int can = 0;
+            e = cudaDeviceCanAccessPeer(&can, m.device, dev0);
+            if (e == cudaSuccess && !can) { rc = fail(NBODY_E_CUDA, "device %d cannot access device %d (no P2P path)", m.device, dev0); break; }
+            if (e == cudaSuccess) {
+                const cudaError_t pe = cudaDeviceEnablePeerAccess(dev0, 0);
+                if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) e = pe;
+                cudaGetLastError();
+            }
+            if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&m.st, cudaStreamNonBlocking);
+        }
+        if (e == cudaSuccess) rc = make_plan(var, prop.multiProcessorCount, 0, m.n_targets, k.n_pad / var->UJ, &m.plan);
+        if (!rc && e == cudaSuccess) e = cudaMalloc(&m.packed, (size_t)k.n_pad * sizeof(float4));
+        if (!rc && e == cudaSuccess) e = cudaMalloc(&m.partial, m.plan.partial_bytes);
+        if (!rc && e == cudaSuccess) e = cudaMalloc(&m.counters, (size_t)m.plan.num_counters * sizeof(unsigned));
+        if (!rc && e == cudaSuccess) e = cudaMemset(m.counters, 0, (size_t)m.plan.num_counters * sizeof(unsigned));
+    }
+    if (!rc && e == cudaSuccess) e = cudaSetDevice(dev0);
+    if (!rc && e == cudaSuccess) e = cudaEventCreateWithFlags(&k.packed_ready, cudaEventDisableTiming);
+    if (rc || e != cudaSuccess) {
+        const std::string keep = g_err;
+        free_cached_multi(k);
+        g_cache_multi.erase(std::make_pair(devs, std::make_pair(n, variant)));
+        cudaSetDevice(dev0);
+        if (rc) { g_err = keep; return rc; }
+        return fail(NBODY_E_CUDA, "multi-device scratch: %s", cudaGetErrorString(e));
+    }
+    k.var = var;
+    *out = &k;
+    return NBODY_OK;
+}
+
+int one_step_multi(CachedMulti* k, float4* dX, void* dA, void* dV, int n, float eps2, float dt, int integ, int va_f3)
+{
+    const int dev0 = k->d[0].device;
+    // snapshot of the step's start in packed form on the first device, then one copy per peer
+    int rc = launch_pack(dX, n, k->d[0].packed, 0, k->n_pad, 0);
+    if (rc) return rc;
+    CU(cudaEventRecord(k->packed_ready, 0));
+    const size_t va_stride = va_f3 ? 12 : 16;
+    for (size_t g = 0; g < k->d.size(); ++g) {
+        const size_t i = (g + 1) % k->d.size();   // the peers first, the first device last (its launch is on the caller's stream)
+        MultiDev& m = k->d[i];
+        CU(cudaSetDevice(m.device));
+        if (i != 0) {
+            CU(cudaStreamWaitEvent(m.st, k->packed_ready, 0));
+            CU(cudaMemcpyPeerAsync(m.packed, m.device, k->d[0].packed, dev0, (size_t)k->n_pad * sizeof(float4), m.st));
+        }
+        ForceArgs a{};
+        a.X = dX + m.t_begin;
+        a.V = reinterpret_cast<float4*>(static_cast<char*>(dV) + va_stride * (size_t)m.t_begin);
+        a.A = reinterpret_cast<float4*>(static_cast<char*>(dA) + va_stride * (size_t)m.t_begin);
+        a.n_targets = m.n_targets;
+        a.src = m.packed;
+        a.ra_begin = 0; a.ra_count = k->n_pad / k->var->UJ;
+        a.partial = m.partial; a.counters = m.counters; a.maxseg = m.plan.maxseg;
+        a.eps2 = eps2; a.dt = dt; a.integ_f64 = integ; a.va_f3 = va_f3;
+        rc = launch_force(k->var, m.plan, a, m.st);
+        if (rc) { cudaSetDevice(dev0); return rc; }
+    }
+    cudaError_t e = cudaSuccess;
+    for (size_t i = 1; i < k->d.size() && e == cudaSuccess; ++i) {
+        e = cudaSetDevice(k->d[i].device);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(k->d[i].st);
+    }
+    cudaSetDevice(dev0);
+    if (e != cudaSuccess) return fail(NBODY_E_CUDA, "multi-device step: %s", cudaGetErrorString(e));
+    return NBODY_OK;
+}
+
+// one in-place step on device arrays, on the current device alone or spread over nbody_set_devices' list
+int inplace_step(float4* dX, void* dA, void* dV, int n, float eps2, float dt, int integ, int va_f3, int variant)
+{
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    if (g_inplace_devices.size() > 1) {
+        CachedMulti* k = nullptr;
+        int rc = get_cached_multi(n, variant, &k);
+        if (rc) return rc;
+        rc = one_step_multi(k, dX, dA, dV, n, eps2, dt, integ, va_f3);
+        if (rc) return rc;
+    } else {
+        Cached* k = nullptr;
+        int rc = get_cached(n, false, &k, variant);
+        if (rc) return rc;
+        rc = one_step_on_device(k, dX, static_cast<float4*>(dA), static_cast<float4*>(dV), n, eps2, dt, integ, 0.0, va_f3);
+        if (rc) return rc;
+    }
+    CU(cudaDeviceSynchronize());   // the reference's simulate() is synchronous (kernel.cu:644)
+    return NBODY_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -443,13 +660,23 @@ int nbody_step_inplace_f4(float* d_bodies4, float* d_accel4, float* d_vel4, int 
     if (!d_bodies4 || !d_accel4 || !d_vel4) return fail(NBODY_E_INVALID, "null device pointer");
     if (n <= 0) return fail(NBODY_E_INVALID, "N must be > 0 (got %d)", n);
     if (!(eps2 > 0.f)) return fail(NBODY_E_INVALID, "eps2 must be > 0");
+    if (!eps2_representable(eps2)) return fail(NBODY_E_INVALID, "eps2 = %g is too small: eps2^3 must be a normal float (eps2 >= %g)", (double)eps2, (double)kMinEps2);
+    return inplace_step((float4*)d_bodies4, d_accel4, d_vel4, n, eps2, dt, NBODY_INTEG_F32, 0, NBODY_VARIANT_AUTO);
+}
+
+int nbody_set_devices(const int* devices, int n)
+{
     std::lock_guard<std::mutex> lk(g_cache_mu);
-    Cached* k = nullptr;
-    int rc = get_cached(n, false, &k);
-    if (rc) return rc;
-    rc = one_step_on_device(k, (float4*)d_bodies4, (float4*)d_accel4, (float4*)d_vel4, n, eps2, dt, 0, 0.0);
-    if (rc) return rc;
-    CU(cudaDeviceSynchronize());   // the reference's simulate() is synchronous (kernel.cu:644)
+    if (!devices || n <= 1) { g_inplace_devices.clear(); return NBODY_OK; }
+    if (n > NBODY_MAX_DEVICES) return fail(NBODY_E_INVALID, "at most %d devices", NBODY_MAX_DEVICES);
+    int ndev = 0;
+    CU(cudaGetDeviceCount(&ndev));
+    for (int i = 0; i < n; ++i) {
+        if (devices[i] < 0 || devices[i] >= ndev) return fail(NBODY_E_INVALID, "device %d not present (%d devices)", devices[i], ndev);
+        for (int j = 0; j < i; ++j)
+            if (devices[j] == devices[i]) return fail(NBODY_E_INVALID, "device %d listed twice", devices[i]);
+    }
+    g_inplace_devices.assign(devices, devices + n);
     return NBODY_OK;
 }
 
@@ -460,6 +687,7 @@ int nbody_step_host_f3(float* h_bodies4, float* h_accel3, float* h_vel3, int n, 
     if (!h_bodies4 || !h_vel3) return fail(NBODY_E_INVALID, "null host pointer");
     if (n <= 0) return fail(NBODY_E_INVALID, "N must be > 0 (got %d)", n);
     if (!(eps2 > 0.0)) return fail(NBODY_E_INVALID, "eps2 must be > 0");
+    if (!eps2_representable((float)eps2)) return fail(NBODY_E_INVALID, "eps2 = %g is too small: eps2^3 must be a normal float (eps2 >= %g)", eps2, (double)kMinEps2);
     std::lock_guard<std::mutex> lk(g_cache_mu);
     Cached* k = nullptr;
     int rc = get_cached(n, true, &k);
@@ -495,14 +723,8 @@ int nbody_step_inplace_opts(float* d_bodies4, void* d_accel, void* d_vel, int n,
     if (!(o->eps2 > 0.f)) return fail(NBODY_E_INVALID, "eps2 must be > 0");
     if (o->integrator != NBODY_INTEG_F32 && o->integrator != NBODY_INTEG_MIXED)
         return fail(NBODY_E_INVALID, "integrator %d not valid for the in-place step", o->integrator);
-    std::lock_guard<std::mutex> lk(g_cache_mu);
-    Cached* k = nullptr;
-    int rc = get_cached(n, false, &k, o->variant);
-    if (rc) return rc;
-    rc = one_step_on_device(k, (float4*)d_bodies4, (float4*)d_accel, (float4*)d_vel, n, o->eps2, o->dt, o->integrator, 0.0, o->va_float3 ? 1 : 0);
-    if (rc) return rc;
-    CU(cudaDeviceSynchronize());
-    return NBODY_OK;
+    if (!eps2_representable(o->eps2)) return fail(NBODY_E_INVALID, "eps2 = %g is too small: eps2^3 must be a normal float (eps2 >= %g)", (double)o->eps2, (double)kMinEps2);
+    return inplace_step((float4*)d_bodies4, d_accel, d_vel, n, o->eps2, o->dt, o->integrator, o->va_float3 ? 1 : 0, o->variant);
 }
 
 void nbody_release_cached(void)
@@ -515,6 +737,8 @@ void nbody_release_cached(void)
         free_cached(kv.second);
     }
     g_cache.clear();
+    for (auto& kv : g_cache_multi) free_cached_multi(kv.second);
+    g_cache_multi.clear();
     release_render_scratch();
     cudaSetDevice(cur);
 }

@@ -13,8 +13,10 @@
 //                  [--flavour simulate|emb|emb-float3]   which launcher of kernel.cuh:2-7 (headless forms)
 //                  [--ppm FILE]                          final frame (the reference's GL draw as CUDA)
 //                  [--save FILE] [--load FILE]           snapshot / resume (with --resident)
-//                  [--gpus G]                            G GPUs of this box from ONE process: each owns N/G targets,
-//                                                        fused P2P exchange, cross-device events as the barrier
+//                  [--gpus G]                            G GPUs of this box from ONE process: with --resident ONE multi-device
+//                                                        context (each device owns N/G targets; --exchange p2p|nccl), else
+//                                                        simulate_set_devices(G): the reference's loop over simulate() with
+//                                                        the caller's arrays on device 0 and the step spread over G devices
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -73,7 +75,7 @@ int main(int argc, char** argv)
     int n = N_BODIES, steps = 10;
     unsigned long long seed = 12345;
     float eps2 = EPS2, dt = DT;
-    std::string ic = "reference", flavour = "simulate", ppm, save, load;
+    std::string ic = "reference", flavour = "simulate", exchange = "p2p", ppm, save, load;
     bool resident = false, host_f3 = false, json = false;
     int gpus = 1;
     for (int i = 1; i < argc; ++i) {
@@ -89,6 +91,7 @@ int main(int argc, char** argv)
         else if (!strcmp(argv[i], "--json")) json = true;
         else if (!strcmp(argv[i], "--gpus")) gpus = atoi(need("--gpus"));
         else if (!strcmp(argv[i], "--flavour")) flavour = need("--flavour");
+        else if (!strcmp(argv[i], "--exchange")) exchange = need("--exchange");
         else if (!strcmp(argv[i], "--ppm")) ppm = need("--ppm");
         else if (!strcmp(argv[i], "--save")) save = need("--save");
         else if (!strcmp(argv[i], "--load")) load = need("--load");
@@ -97,6 +100,9 @@ int main(int argc, char** argv)
     if (n <= 0 || steps < 0) { fprintf(stderr, "bad --n / --steps\n"); return 2; }
     if ((!save.empty() || !load.empty()) && !resident) { fprintf(stderr, "--save / --load need --resident\n"); return 2; }
     if (flavour != "simulate" && flavour != "emb" && flavour != "emb-float3") { fprintf(stderr, "unknown --flavour %s\n", flavour.c_str()); return 2; }
+    if (exchange != "p2p" && exchange != "nccl") { fprintf(stderr, "unknown --exchange %s\n", exchange.c_str()); return 2; }
+    if (gpus < 1 || gpus > NBODY_MAX_DEVICES) { fprintf(stderr, "bad --gpus\n"); return 2; }
+    if (gpus > 1 && host_f3) { fprintf(stderr, "--host-f3 is the host-pointer flavour: one GPU\n"); return 2; }
     const size_t size4 = sizeof(float4) * (size_t)n;
 
     float4 *bodies, *velocity, *accelerations;   // pinned, main.cpp:250-252
@@ -114,59 +120,30 @@ int main(int argc, char** argv)
 
     int rc = 0;
     float ms = -1.f, ms_first = -1.f, ms_steady = -1.f;
-    if (gpus > 1) {
-        // One process, G contexts (rank g on device g).  The reference is single-GPU (kernel.cu:630 asks for device 0);
-        // this is the C++ face of the fused exchange: every step is ONE kernel per GPU whose epilogue stores the new
-        // positions into every GPU's next source buffer, and "all GPUs have finished step s" is expressed with events
-        // (each stream waits for every other GPU's event) -- no collective library, no host synchronisation in the loop.
-        std::vector<nbody_ctx*> ctx(gpus, nullptr);
-        std::vector<cudaStream_t> st(gpus);
-        std::vector<cudaEvent_t> ev(gpus);
-        bool ok = true;
-        for (int g = 0; g < gpus && ok; ++g) {
-            nbody_params p;
-            nbody_params_default(&p);
-            p.n_bodies = n; p.eps2 = eps2; p.dt = dt; p.rank = g; p.world = gpus; p.device = g;
-            ok = nbody_create(&ctx[g], &p) == NBODY_OK && nbody_upload(ctx[g], (float*)bodies, (float*)velocity) == NBODY_OK &&
-                 cudaSetDevice(g) == cudaSuccess && cudaStreamCreateWithFlags(&st[g], cudaStreamNonBlocking) == cudaSuccess &&
-                 cudaEventCreateWithFlags(&ev[g], cudaEventDisableTiming) == cudaSuccess;
+    if (gpus > 1 && resident) {
+        // ONE context spanning G devices (nbody_params.n_devices): the library owns the per-device shards, the peer
+        // mapping, the exchange (--exchange p2p: fused into the step kernel, in-kernel flag barrier; nccl: ncclAllGather
+        // on a second stream) -- the host code below is the single-GPU --resident branch with a device list.
+        nbody_params p;
+        nbody_params_default(&p);
+        p.n_bodies = n; p.eps2 = eps2; p.dt = dt; p.n_devices = gpus;
+        p.exchange = exchange == "nccl" ? NBODY_EXCHANGE_NCCL : NBODY_EXCHANGE_P2P;
+        for (int g = 0; g < gpus && g < NBODY_MAX_DEVICES; ++g) p.devices[g] = g;
+        nbody_ctx* ctx = nullptr;
+        if (nbody_create(&ctx, &p) || (load.empty() ? nbody_upload(ctx, (float*)bodies, (float*)velocity) : nbody_snapshot_load(ctx, load.c_str()))) {
+            std::cerr << nbody_last_error() << std::endl;
+            return EXIT_FAILURE;
         }
-        for (int g = 0; g < gpus && ok; ++g)
-            for (int h = 0; h < gpus && ok; ++h) {
-                void *b0, *b1;
-                if (h != g) ok = nbody_shard_buffers(ctx[h], &b0, &b1) == NBODY_OK && nbody_shard_attach_ptr(ctx[g], h, b0, b1) == NBODY_OK;
-            }
-        if (!ok) { std::cerr << nbody_last_error() << std::endl; return EXIT_FAILURE; }
-        cudaEvent_t t0, t1;
-        cudaSetDevice(0);
-        cudaEventCreate(&t0); cudaEventCreate(&t1);
         printf("Starting the simulation...\n");
-        cudaEventRecord(t0, st[0]);
-        for (int s = 0; s < steps && ok; ++s) {
-            for (int g = 0; g < gpus && ok; ++g) {
-                cudaSetDevice(g);
-                ok = nbody_shard_step_fused_async(ctx[g], st[g]) == NBODY_OK && cudaEventRecord(ev[g], st[g]) == cudaSuccess;
-            }
-            for (int g = 0; g < gpus && ok; ++g) {      // barrier: nobody starts step s+1 before everybody finished step s
-                cudaSetDevice(g);
-                for (int h = 0; h < gpus; ++h)
-                    if (h != g) ok = ok && cudaStreamWaitEvent(st[g], ev[h], 0) == cudaSuccess;
-            }
-        }
-        cudaSetDevice(0);
-        cudaEventRecord(t1, st[0]);
-        for (int g = 0; g < gpus; ++g) { cudaSetDevice(g); ok = ok && cudaStreamSynchronize(st[g]) == cudaSuccess; }
-        if (!ok) { std::cerr << "multi-GPU run failed: " << nbody_last_error() << " / " << cudaGetErrorString(cudaGetLastError()) << std::endl; rc = EXIT_FAILURE; }
+        if (nbody_step(ctx, steps)) { std::cerr << nbody_last_error() << std::endl; rc = EXIT_FAILURE; }
         else printf("Simulation complete\n");
-        cudaSetDevice(0);
-        cudaEventElapsedTime(&ms, t0, t1);
-        for (int g = 0; g < gpus; ++g) {
-            int b = 0, cnt = 0;
-            nbody_owned_range(ctx[g], &b, &cnt);
-            nbody_download(ctx[g], (float*)(bodies + b), (float*)(velocity + b), (float*)(accelerations + b));
-        }
-        for (int g = 0; g < gpus; ++g) { nbody_destroy(ctx[g]); cudaSetDevice(g); cudaStreamDestroy(st[g]); cudaEventDestroy(ev[g]); }
-        cudaSetDevice(0);
+        nbody_elapsed_ms(ctx, &ms);
+        int timed_out = 0;
+        nbody_shard_barrier_timeouts(ctx, &timed_out);
+        if (timed_out) { std::cerr << "cross-GPU barrier timed out " << timed_out << " time(s): state invalid" << std::endl; rc = EXIT_FAILURE; }
+        nbody_download(ctx, (float*)bodies, (float*)velocity, (float*)accelerations);
+        if (!save.empty() && nbody_snapshot_save(ctx, save.c_str())) { std::cerr << nbody_last_error() << std::endl; rc = EXIT_FAILURE; }
+        nbody_destroy(ctx);
     } else if (host_f3) {
         // headless-directory flavour: host pointers, float3 velocity (its constants: EPS2 0.002, DT 0.01)
         float3* v3 = new float3[n];
@@ -206,6 +183,9 @@ int main(int argc, char** argv)
         cudaMalloc((void**)&d_bodies, size4);
         cudaMemcpy(d_bodies, bodies, size4, cudaMemcpyHostToDevice);
         simulate_set_parameters(eps2, dt);
+        try {
+            simulate_set_devices(gpus);   // the one added line that lets main.cpp's loop use every GPU of the box
+        } catch (const std::exception& e) { std::cerr << e.what() << std::endl; return EXIT_FAILURE; }
         cudaEvent_t e0, e1, ef;
         cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&ef);
         cudaEventRecord(e0);
@@ -253,10 +233,10 @@ int main(int argc, char** argv)
         const double inter = (double)n * (double)n * steps;
         printf("{\"n\": %d, \"steps\": %d, \"ic\": \"%s\", \"flavour\": \"%s\", \"device_ms\": %.4f, \"g_interactions_per_s\": %.3f, "
                "\"first_call_ms\": %.4f, \"steady_ms_per_step\": %.4f, \"steady_g_interactions_per_s\": %.3f, "
-               "\"checksum_x\": %.9e, \"checksum_v\": %.9e, \"launches\": %lld}\n",
-               n, steps, ic.c_str(), gpus > 1 ? "multi-gpu fused exchange" : host_f3 ? "host-f3" : resident ? "resident" : flavour.c_str(), ms, ms > 0 ? inter / (ms * 1e-3) / 1e9 : 0.0,
+               "\"checksum_x\": %.9e, \"checksum_v\": %.9e, \"launches\": %lld, \"gpus\": %d, \"exchange\": \"%s\"}\n",
+               n, steps, ic.c_str(), host_f3 ? "host-f3" : resident ? "resident" : flavour.c_str(), ms, ms > 0 ? inter / (ms * 1e-3) / 1e9 : 0.0,
                ms_first, ms_steady, ms_steady > 0 ? (double)n * (double)n / (ms_steady * 1e-3) / 1e9 : 0.0,
-               checksum(bodies, n), checksum(velocity, n), nbody_launch_count());
+               checksum(bodies, n), checksum(velocity, n), nbody_launch_count(), gpus, gpus > 1 && resident ? exchange.c_str() : gpus > 1 ? "set_devices" : "none");
     }
     nbody_release_cached();
     cudaFreeHost(bodies); cudaFreeHost(velocity); cudaFreeHost(accelerations);

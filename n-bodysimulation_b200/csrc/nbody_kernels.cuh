@@ -65,8 +65,8 @@ struct ForceArgs {
                           // flavour), 2: mixed (reduction flavours, kernel.cu:455-463: double half-kick, float drift)
     int va_f3;            // 1: V and A are packed float3 arrays (FLOAT_3 build of the reference, main.cpp:233-269)
     double dt64;
-    float k_one, k_negzero;   // 1.0f and -0.0f as run-time values (MODE 2 keeps ptxas from folding x*1+y)
-    // optional: CTA 0 records {clock64, globaltimer} at entry and exit -> SM clock actually run at
+    // optional: CTA 0 records {clock64, globaltimer} at entry and exit -> SM clock actually run at;
+    // clk[4] += ns its thread 0 spent in the cross-GPU flag wait, clk[5] = the longest single wait, clk[6] = waits
     unsigned long long* clk;
 };
 
@@ -156,10 +156,10 @@ __device__ __forceinline__ void integrate_one(const ForceArgs& a, int gi, bool v
 // worker that owns linear unit u when U units are cut into W equal ranges
 __device__ __forceinline__ int unit_owner(u64 u, u64 U, u64 W) { return (int)(((u + 1) * W - 1) / U); }
 
-// MODE: 0 scalar FFMA | 1 packed FADD2/FMUL2/FFMA2 | 2 packed, every op issued as FFMA2
-//       (x*1+y, x*y-0: bit-identical results) | 3 packed + source pairs prefetched one group ahead
-//       | 4 packed + only the next group's FIRST pair prefetched | 5, 6 packed, same arithmetic in another
-//       source order (targets reversed / target-outer): ptxas' register allocation differs by a few per cent
+// MODE: 0 scalar FFMA | 1 packed FADD2/FMUL2/FFMA2 | 5, 6, 7, 8 packed, the same arithmetic in another source
+//       order (5 targets reversed, 6 target-outer, 7 z first, 8 both 5 and 7): every target's sums are formed by
+//       the same operations in the same order, so the results are bit-identical; only ptxas' register
+//       allocation differs (worth a few per cent, see tuned_large_variant in nbody_engine.cu).
 // CS / CMODE: thread-block clusters (launch attribute clusterDim = CS).
 //   CMODE 1 "multicast": the CS CTAs of a cluster own CS neighbouring target tiles and stream
 //           the SAME source units; CTA r fetches slice r of each unit and TMA-multicasts it
@@ -261,6 +261,12 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
                 }
             }
             __threadfence_system();
+            if (a.clk && blockIdx.x == 0) {   // how long this GPU stood waiting for its peers (all CTAs start together)
+                const unsigned long long waited = globaltimer_ns() - t0;
+                a.clk[4] += waited;
+                if (waited > a.clk[5]) a.clk[5] = waited;
+                a.clk[6] += 1ull;
+            }
         }
         while (kf < kLookahead && issue()) {}
     }
@@ -298,24 +304,21 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
             const int s = k & (kStages - 1);
             mbar_wait(bar_full + 8 * s, (k / kStages) & 1);
             const ulonglong2* sp = reinterpret_cast<const ulonglong2*>(smem_raw + s * kStageBytes);
-            const u64 one2 = pack2(a.k_one, a.k_one), negz2 = pack2(a.k_negzero, a.k_negzero);
-            auto ADD2 = [&](u64 x, u64 y) { return MODE == 2 ? fma2(x, one2, y) : add2(x, y); };
-            auto MUL2 = [&](u64 x, u64 y) { return MODE == 2 ? fma2(x, y, negz2) : mul2(x, y); };
             // two interactions (one source pair) against every target held by this thread
             auto interact2 = [&](const ulonglong2 xy, const ulonglong2 zm) {
 #pragma unroll
                 for (int tt = 0; tt < T; ++tt) {
                     const int t = (MODE == 5 || MODE == 8) ? T - 1 - tt : tt;   // MODE 5/8: same arithmetic, targets visited in reverse
                     u64 dx, dy, dz;
-                    if (MODE == 7 || MODE == 8) { dz = ADD2(zm.x, nz[t]); dy = ADD2(xy.y, ny[t]); dx = ADD2(xy.x, nx[t]); }   // z first
-                    else { dx = ADD2(xy.x, nx[t]); dy = ADD2(xy.y, ny[t]); dz = ADD2(zm.x, nz[t]); }
+                    if (MODE == 7 || MODE == 8) { dz = add2(zm.x, nz[t]); dy = add2(xy.y, ny[t]); dx = add2(xy.x, nx[t]); }   // z first
+                    else { dx = add2(xy.x, nx[t]); dy = add2(xy.y, ny[t]); dz = add2(zm.x, nz[t]); }
                     u64 r2 = fma2(dx, dx, eps2p);
                     r2 = fma2(dy, dy, r2);
                     r2 = fma2(dz, dz, r2);
-                    const u64 d3 = MUL2(MUL2(r2, r2), r2);      // (r^2+eps2)^3, as kernel.cu:20
+                    const u64 d3 = mul2(mul2(r2, r2), r2);      // (r^2+eps2)^3, as kernel.cu:20
                     float lo, hi;
                     unpack2(d3, lo, hi);
-                    const u64 sc = MUL2(pack2(rsqrt_mufu(lo), rsqrt_mufu(hi)), zm.y);
+                    const u64 sc = mul2(pack2(rsqrt_mufu(lo), rsqrt_mufu(hi)), zm.y);
                     if (MODE == 7 || MODE == 8) { az[t] = fma2(dz, sc, az[t]); ay[t] = fma2(dy, sc, ay[t]); ax[t] = fma2(dx, sc, ax[t]); }
                     else { ax[t] = fma2(dx, sc, ax[t]); ay[t] = fma2(dy, sc, ay[t]); az[t] = fma2(dz, sc, az[t]); }
                 }
@@ -344,35 +347,6 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
                             az[t] = fma2(dz, sc, az[t]);
                         }
                     }
-                }
-            } else if (MODE == 3) {
-                ulonglong2 cxy[UNROLL], czm[UNROLL];
-#pragma unroll
-                for (int q = 0; q < UNROLL; ++q) { cxy[q] = sp[2 * q]; czm[q] = sp[2 * q + 1]; }
-#pragma unroll 1
-                for (int p = 0; p < UJ / 2; p += UNROLL) {
-                    ulonglong2 nxy[UNROLL], nzm[UNROLL];
-                    const int pn = (p + UNROLL < UJ / 2) ? p + UNROLL : p;   // last group re-reads itself
-#pragma unroll
-                    for (int q = 0; q < UNROLL; ++q) { nxy[q] = sp[2 * (pn + q)]; nzm[q] = sp[2 * (pn + q) + 1]; }
-#pragma unroll
-                    for (int q = 0; q < UNROLL; ++q) interact2(cxy[q], czm[q]);
-#pragma unroll
-                    for (int q = 0; q < UNROLL; ++q) { cxy[q] = nxy[q]; czm[q] = nzm[q]; }
-                }
-            } else if (MODE == 4) {
-                // first pair of the NEXT group is loaded while this group is computed, so no
-                // LDS latency is exposed at the loop top (r1 source-page profile: 26 of 646
-                // cycles per iteration were short-scoreboard stalls on that load).  The last
-                // group reads 32 B past the stage (next stage / barrier words): discarded.
-                ulonglong2 cxy = sp[0], czm = sp[1];
-#pragma unroll 1
-                for (int p = 0; p < UJ / 2; p += UNROLL) {
-                    const ulonglong2 nxy = sp[2 * (p + UNROLL)], nzm = sp[2 * (p + UNROLL) + 1];
-                    interact2(cxy, czm);
-#pragma unroll
-                    for (int q = 1; q < UNROLL; ++q) interact2(sp[2 * (p + q)], sp[2 * (p + q) + 1]);
-                    cxy = nxy; czm = nzm;
                 }
             } else {
 #pragma unroll 1

@@ -120,6 +120,28 @@ int render_on_device(const float4* dX, int n, const nbody_view* v, unsigned long
     return NBODY_OK;
 }
 
+int group_render(nbody_ctx* c, const nbody_view* v, unsigned char* h_rgba);   // nbody_group.inl
+
+// frame of n bodies in device array X (on c's device) into a host buffer, on c's stream with c's frame scratch
+int render_arrays(nbody_ctx* c, const float4* X, int n, const nbody_view* v, unsigned char* h_rgba)
+{
+    int rc = set_device(c);
+    if (rc) return rc;
+    const size_t npix = (size_t)v->width * v->height, bytes = npix * 4;
+    if (c->frame_bytes < bytes) {   // frame + its keys live with the context (its stream orders their use)
+        cudaFree(c->frame); cudaFree(c->frame_keys);
+        c->frame = nullptr; c->frame_keys = nullptr; c->frame_bytes = 0;
+        CU(cudaMalloc(&c->frame, bytes));
+        CU(cudaMalloc(&c->frame_keys, npix * sizeof(unsigned long long)));
+        c->frame_bytes = bytes;
+    }
+    rc = render_on_device(X, n, v, c->frame_keys, c->frame, c->stream);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(h_rgba, c->frame, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return NBODY_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -162,24 +184,11 @@ int nbody_render(nbody_ctx* c, const nbody_view* v, unsigned char* h_rgba)
 {
     TRACE_CALL();
     if (!c || !h_rgba) return fail(NBODY_E_INVALID, "null argument");
-    if (c->p.world != 1) return fail(NBODY_E_STATE, "nbody_render needs an unsharded context (a shard holds only its own bodies)");
     int rc = check_view(v);
     if (rc) return rc;
-    rc = set_device(c);
-    if (rc) return rc;
-    const size_t npix = (size_t)v->width * v->height, bytes = npix * 4;
-    if (c->frame_bytes < bytes) {   // frame + its keys live with the context (its stream orders their use)
-        cudaFree(c->frame); cudaFree(c->frame_keys);
-        c->frame = nullptr; c->frame_keys = nullptr; c->frame_bytes = 0;
-        CU(cudaMalloc(&c->frame, bytes));
-        CU(cudaMalloc(&c->frame_keys, npix * sizeof(unsigned long long)));
-        c->frame_bytes = bytes;
-    }
-    rc = render_on_device(c->X, c->n, v, c->frame_keys, c->frame, c->stream);
-    if (rc) return rc;
-    CU(cudaMemcpyAsync(h_rgba, c->frame, bytes, cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaStreamSynchronize(c->stream));
-    return NBODY_OK;
+    if (!c->kids.empty()) return group_render(c, v, h_rgba);
+    if (c->p.world != 1) return fail(NBODY_E_STATE, "nbody_render needs an unsharded context (a shard holds only its own bodies)");
+    return render_arrays(c, c->X, c->n, v, h_rgba);
 }
 
 int nbody_write_ppm(const char* path, const unsigned char* rgba, int width, int height)

@@ -59,11 +59,15 @@ class ShardedSimulation:
         self.torch, self.dist = torch, dist
         self.sim, self.rank, self.world, self.group = sim, rank, world, group
         self.device = device
-        self.overlap = overlap and device is not None and torch.device(device).type == "cuda"
+        self.on_gpu = device is not None and torch.device(device).type == "cuda"
+        self.overlap = overlap and self.on_gpu
         self._views = {}
-        if self.overlap:
+        if self.on_gpu:
+            # always an explicit torch stream: the C ABI maps stream 0 to the context's own non-blocking stream, which
+            # nothing orders against torch's collectives.  overlap=False: ONE stream for kernels and collectives
+            # (fully serialised); overlap=True: the gather runs on a second stream beside the own-slice kernel.
             self.compute = torch.cuda.Stream(device=device)
-            self.comm = torch.cuda.Stream(device=device)
+            self.comm = torch.cuda.Stream(device=device) if self.overlap else self.compute
         self.steps_done = 0
         assert exchange in ("nccl", "p2p")
         assert barrier in ("auto", "device", "collective")
@@ -123,31 +127,38 @@ class ShardedSimulation:
         """one step; on return the current source buffer holds everyone's new positions
         (work may still be in flight on self.compute / self.comm when overlapping)"""
         if self.world == 1:
-            self.sim.shard_local_async(self.compute.cuda_stream if self.overlap else 0)
+            self.sim.shard_local_async(self.compute.cuda_stream if self.on_gpu else 0)
             self.steps_done += 1
             return
         if self.exchange == "p2p":
             torch = self.torch
             # barrier after the step: my stores have left (kernel complete) and every peer's have landed
             # before the next step reads them; also nobody overwrites a buffer a peer is still reading
-            if self.device is None or torch.device(self.device).type != "cuda":
+            if not self.on_gpu:
                 self.sim.shard_step_fused_async(0)
                 self.dist.all_reduce(self._flag, group=self.group)
             else:
-                st = self.compute if self.overlap else torch.cuda.current_stream(self.device)
+                st = self.compute
                 self.sim.shard_step_fused_async(st.cuda_stream)
                 if self.barrier != "device":
                     with torch.cuda.stream(st):
                         self.dist.all_reduce(self._flag, group=self.group)
             self.steps_done += 1
             return
-        if not self.overlap:
+        if not self.on_gpu:
             self.sim.shard_local_async(0)
             self.sim.shard_remote_async(0)
             self.gather_current()
             self.steps_done += 1
             return
         torch = self.torch
+        if not self.overlap:   # one stream: local, remote, gather in program order
+            self.sim.shard_local_async(self.compute.cuda_stream)
+            self.sim.shard_remote_async(self.compute.cuda_stream)
+            with torch.cuda.stream(self.compute):
+                self.gather_current()
+            self.steps_done += 1
+            return
         # 1. own x own on the compute stream; needs only this rank's slice, which the previous
         #    remote kernel (same stream) wrote -- so it runs while the gather is in flight
         self.sim.shard_local_async(self.compute.cuda_stream)
@@ -161,6 +172,15 @@ class ShardedSimulation:
         self.steps_done += 1
 
     def synchronize(self) -> None:
-        if self.overlap:
+        if self.on_gpu:
             self.compute.synchronize()
             self.comm.synchronize()
+
+    def quiesce(self) -> None:
+        """every rank has finished everything it launched and nobody has started anything new: required around
+        nbody_upload / nbody_snapshot_load on a context whose buffers peers store into (fused exchange)"""
+        self.synchronize()
+        if self.world > 1:
+            self.dist.barrier(group=self.group)
+            if self.on_gpu:
+                self.torch.cuda.synchronize(self.device)

@@ -225,6 +225,18 @@ int oracle_verify_still_bodies(const float *v, const float *x, int N)
     return bad;
 }
 
+/* Thread count of every OpenMP region that follows in this process (ours and, sharing the runtime, the
+ * reference's own CPU_compute in oracle/_ref/libref_cpu_omp*.so).  bench.py sets it to all host cores
+ * explicitly: torchrun exports OMP_NUM_THREADS=1 to its workers. */
+void oracle_set_num_threads(int n)
+{
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int oracle_num_threads(void)
 {
 #ifdef _OPENMP

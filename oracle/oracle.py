@@ -44,6 +44,20 @@ def num_threads() -> int:
     return int(_lib.oracle_num_threads())
 
 
+def host_cores() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def set_num_threads(n: int | None = None) -> int:
+    """OpenMP threads of every checker / reference-CPU call that follows (default: all host cores this process
+    may run on, whatever OMP_NUM_THREADS says -- torchrun sets it to 1 in its workers)"""
+    _lib.oracle_set_num_threads(C.c_int(n or host_cores()))
+    return num_threads()
+
+
 def pair(bi, bj, ai, eps2=0.002):
     ai = np.array(ai, np.float32)
     _lib.oracle_pair_f32(_fp(np.asarray(bi, np.float32)), _fp(np.asarray(bj, np.float32)), _fp(ai), C.c_float(eps2))

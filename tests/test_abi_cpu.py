@@ -49,9 +49,41 @@ def test_argument_validation(nb):
         setattr(q, field, bad)
         assert nb.lib.nbody_create(C.byref(h), C.byref(q)) == -1, field
         assert nb.lib.nbody_last_error()
+    # eps2 whose cube is subnormal: MUFU.RSQ would flush it and turn the self term into 0 * inf (the reference's
+    # 1/sqrtf stays finite there) -- rejected, not answered with NaNs; the bound itself (2^-42) is accepted up to
+    # the point where a device is needed
+    q = nb.NBodyParams.from_buffer_copy(p)
+    q.eps2 = 1e-13
+    assert nb.lib.nbody_create(C.byref(h), C.byref(q)) == -1 and b"too small" in nb.lib.nbody_last_error()
+    assert nb.lib.nbody_step_inplace_f4(1, 1, 1, 16, 1e-13, 0.1) == -1
+    q.eps2 = 2.0 ** -42
+    assert nb.lib.nbody_create(C.byref(h), C.byref(q)) in (0, -2)   # valid argument: succeeds on a GPU, NBODY_E_CUDA without
+    if h.value:
+        nb.lib.nbody_destroy(h)
     assert nb.lib.nbody_step_inplace_f4(None, None, None, 16, 0.002, 0.1) == -1
     assert nb.lib.nbody_step_inplace_f4(1, 1, 1, 0, 0.002, 0.1) == -1
     assert nb.lib.nbody_step_host_f3(None, None, None, 4, 0.002, 0.01) == -1
+
+
+def test_multi_device_parameters_are_validated_on_the_host(nb):
+    # nbody_params.n_devices > 1: ONE context over several GPUs ("nbody_create takes a device list")
+    h = C.c_void_p()
+    p = nb.NBodyParams()
+    nb.lib.nbody_params_default(C.byref(p))
+    assert (p.n_devices, p.exchange, p.deterministic) == (0, nb.NBODY_EXCHANGE_P2P, 0)
+    q = nb.NBodyParams.from_buffer_copy(p)
+    q.n_devices = nb.NBODY_MAX_DEVICES + 1
+    assert nb.lib.nbody_create(C.byref(h), C.byref(q)) == -1
+    q.n_devices, q.world, q.rank = 2, 2, 1                     # a group is the whole system
+    assert nb.lib.nbody_create(C.byref(h), C.byref(q)) == -1 and b"whole system" in nb.lib.nbody_last_error()
+    q.world, q.rank, q.exchange = 1, 0, 7
+    assert nb.lib.nbody_create(C.byref(h), C.byref(q)) == -1 and b"exchange" in nb.lib.nbody_last_error()
+    assert nb.lib.nbody_group_info(None, None, None, None) == -1
+    assert nb.lib.nbody_shard_barrier_wait_ns(None, None, None, None, 0) == -1
+    # nbody_set_devices: list checks need the device count, so without a GPU the call reports NBODY_E_CUDA; clearing works anywhere
+    assert nb.lib.nbody_set_devices(None, 0) == 0
+    arr = (C.c_int * 17)(*range(17))
+    assert nb.lib.nbody_set_devices(arr, 17) == -1
 
 
 def test_no_cpu_fallback(nb):

@@ -139,7 +139,7 @@ def test_opts_step_with_cluster_variants_agrees_with_default(cuda, nb, oracle):
     n = 20000
     x0 = nb.ic_uniform(n, seed=24)
     ref = None
-    for variant in (0, 60, 64, 65):          # auto | C2 multicast | C2 / C4 j-split with DSMEM reduction
+    for variant in (0, 60, 64):              # auto | C2 multicast | C2 j-split with DSMEM reduction
         dx, dv, da = torch.from_numpy(x0).cuda(), torch.zeros(n, 4, device="cuda"), torch.zeros(n, 4, device="cuda")
         nb.simulate_opts(dx, da, dv, n, variant=variant)
         a = da.cpu().numpy()
@@ -295,13 +295,15 @@ def test_large_contexts_pick_their_kernel_by_measurement(cuda, nb):
     with nb.Simulation(70000) as sim:                          # >= 64 k bodies: resolved through the tuner
         name = sim.info()["variant_name"]
     rep = nb.autotune_report()
-    assert name.startswith(("T6_NT256", "T8_NT256"))
+    assert name.startswith("T6_NT256_UJ512")                   # 512-body units from 64 k sources on
     cands = dict(item.split(":") for item in rep.split())
     assert len(cands) >= 4 and all(0.1 < float(ms[:-2]) < 50 for ms in cands.values()), rep
     chosen = [k for k in cands if nb.variants()[int(k)].split(":")[0] == name]
     assert len(chosen) == 1
-    # the report rounds to 1 us: the chosen kernel is the fastest up to that rounding
-    assert float(cands[chosen[0]][:-2]) <= min(float(ms[:-2]) for ms in cands.values()) * 1.005 + 0.0015, rep
+    # the report rounds to 1 us: the chosen kernel is the fastest OF ITS FAMILY (same tile shape and unit size, hence
+    # bit-identical results whichever wins) up to that rounding
+    family = [float(ms[:-2]) for k, ms in cands.items() if nb.variants()[int(k)].startswith("T6_NT256_UJ512")]
+    assert len(family) == 3 and float(cands[chosen[0]][:-2]) <= min(family) * 1.005 + 0.0015, rep
 
 
 def test_mid_size_contexts_pick_tile_shape_by_unit_balance(cuda, nb, oracle):
