@@ -277,8 +277,9 @@ def run_reference(args):
 # ---- helpers of our arm ------------------------------------------------------------------------------
 def norm_rel(p, q):
     import numpy as np
-    d = np.linalg.norm((p.astype(np.float64) - q.astype(np.float64))[:, :3], axis=1)
-    den = np.linalg.norm(q.astype(np.float64)[:, :3], axis=1)
+    p, q = np.asarray(p, np.float64)[:, :3], np.asarray(q, np.float64)[:, :3]
+    d = np.linalg.norm(p - q, axis=1)
+    den = np.linalg.norm(q, axis=1)
     return d / np.where(den > 0, den, 1.0)
 
 
