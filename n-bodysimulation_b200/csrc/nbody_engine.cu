@@ -64,7 +64,7 @@ struct Variant {
     int cs, cmode;   // cluster size (1 = none); 1 = TMA multicast of source units, 2 = j-split + DSMEM reduction
     void (*kernel)(const ForceArgs);
     int small = 0;   // 1: small_kernel (T = targets per CTA, sources split over the CTA's threads, shuffle reduction)
-    size_t smem() const { return small ? 0 : (size_t)kStages * UJ * 16 + 16 * kStages + 16 + (cmode == 2 ? (size_t)TI() * 16 : 0); }
+    size_t smem() const { return small ? 0 : (size_t)kStages * UJ * 16 + 16 * kStages + 16 + (cmode == 2 ? (size_t)TI() * 16 : 0) + fold_bytes(T, NT, packed != 0); }
     int TI() const { return small ? T : T * NT; }
     int TS() const { return cmode == 1 ? TI() * cs : TI(); }          // targets per worker tile
 };
@@ -86,21 +86,20 @@ const Variant kVariants[] = {
     VARIANT(3, 2, 256, 256, 8, 1, 3),        // few targets of many sources (a shard of a big system): 3 CTAs/SM
     VARIANT(9, 4, 256, 256, 4, 0, 2),        // scalar FFMA exemplar
     VARIANT(12, 1, 128, 64, 8, 1, 8),        // fewer than 2 048 targets of many sources
-    // large N, 256-body units (12 k .. 64 k sources): one arithmetic, four source orders
-    VARIANT(45, 6, 256, 256, 2, 1, 1),
-    VARIANT(90, 6, 256, 256, 2, 5, 1),
+    // large N, 256-body units (12 k .. 64 k sources): one arithmetic, three source orders
+    VARIANT(90, 6, 256, 256, 2, 18, 1),
     VARIANT(97, 6, 256, 256, 2, 7, 1),
     VARIANT(98, 6, 256, 256, 2, 8, 1),
     // large N, 512-body units (>= 64 k sources): one arithmetic, three source orders
-    VARIANT(101, 6, 256, 512, 2, 5, 1),
+    VARIANT(101, 6, 256, 512, 2, 8, 1),
     VARIANT(102, 6, 256, 512, 2, 7, 1),
-    VARIANT(105, 6, 256, 512, 2, 1, 1),
+    VARIANT(105, 6, 256, 512, 2, 18, 1),
     // mid-size N (cost model in mid_variant): T8 tiles and 64- / 128-body units
     VARIANT(93, 8, 256, 256, 2, 6, 1),
     VARIANT(110, 8, 256, 128, 2, 6, 1),
     VARIANT(111, 8, 256, 64, 2, 6, 1),
-    VARIANT(112, 6, 256, 128, 2, 5, 1),
-    VARIANT(113, 6, 256, 64, 2, 5, 1),
+    VARIANT(112, 6, 256, 128, 2, 18, 1),
+    VARIANT(113, 6, 256, 64, 2, 18, 1),
     // thread-block-cluster exemplars (opt-in; measured neutral / slower, profiles/r1_ncu_cluster_evidence.md):
     // m1 = TMA multicast of source units, m2 = j-split with DSMEM reduction
     CVARIANT(60, 6, 256, 256, 2, 1, 1, 2, 1),
@@ -109,6 +108,11 @@ const Variant kVariants[] = {
     SVARIANT(82, 4, 128, 2),
     SVARIANT(85, 2, 128, 4),
 #ifdef NBODY_SWEEP_VARIANTS
+    VARIANT(45, 6, 256, 256, 2, 1, 1),       // x,y,z source order: 2 % slower than the orders above once the sums are folded
+    VARIANT(46, 6, 256, 256, 2, 5, 1),
+    VARIANT(106, 6, 256, 512, 2, 1, 1),
+    VARIANT(107, 6, 256, 512, 2, 5, 1),
+    VARIANT(129, 6, 256, 1024, 2, 7, 1),
     VARIANT(1, 4, 256, 256, 4, 1, 2),
     VARIANT(2, 2, 256, 256, 4, 1, 4),
     VARIANT(4, 4, 128, 256, 4, 1, 4),
@@ -136,8 +140,7 @@ const Variant kVariants[] = {
     VARIANT(91, 6, 256, 256, 2, 6, 1),
     VARIANT(92, 8, 256, 256, 2, 5, 1),
     VARIANT(96, 8, 256, 512, 2, 6, 1),
-    VARIANT(103, 6, 256, 1024, 2, 5, 1),
-    VARIANT(104, 6, 256, 1024, 2, 1, 1),
+    VARIANT(103, 6, 256, 1024, 2, 18, 1),
     VARIANT(114, 4, 256, 128, 4, 1, 2),
     VARIANT(115, 8, 256, 128, 2, 1, 1),
     CVARIANT(61, 6, 256, 256, 2, 1, 1, 4, 1),
@@ -178,7 +181,7 @@ int static_variant(int n_targets, int n_sources, int sms, bool* measured)
         return 82;                       // 4 targets / CTA
     }
     if (n_targets >= 12288 && n_sources < 65536) return mid_variant(n_targets, n_sources, sms);
-    if (n_targets >= 12288) { *measured = true; return n_sources < 65536 ? 45 : 101; }
+    if (n_targets >= 12288) { *measured = true; return n_sources < 65536 ? 90 : 101; }
     if (n_targets >= 2048) return 3;     // T2 x 256 threads, 3 CTAs/SM
     return 12;                           // T1 x 128 threads, 64-body units
 }
@@ -316,7 +319,7 @@ int launch_pack(const float4* X, int n, float4* packed, int off, int n_cover, cu
 // the RESULT does not depend on which one wins: bit-identical across processes, boxes and ranks
 // (tests/test_parity_gpu.py::test_tuner_candidates_are_bit_identical).  NBODY_LARGE_VARIANT=<id> in the
 // environment overrides; nbody_params.deterministic = 1 skips the timing and takes the first of the family.
-const int kTuneCandidates[] = {45, 90, 97, 98, 101, 102, 105};
+const int kTuneCandidates[] = {90, 97, 98, 101, 102, 105};
 constexpr int kTuneBodies = 49152;   // whole T6 tiles (1536): 0.9 ms per launch
 std::mutex g_tune_mu;
 std::map<int, std::pair<int, int>> g_tuned;   // device -> (best with 256-body units, best overall)
@@ -327,11 +330,11 @@ int tuned_large_variant(int n_sources, bool deterministic)
     // 512-body units win at N >= 64 k (fewer barrier round trips) but cut a 16 k-body step into too few pieces
     const bool small_units = n_sources < 65536;
     int dev = 0;
-    if (deterministic || cudaGetDevice(&dev) != cudaSuccess) return small_units ? 45 : 101;
+    if (deterministic || cudaGetDevice(&dev) != cudaSuccess) return small_units ? 90 : 101;
     std::lock_guard<std::mutex> lk(g_tune_mu);
     auto it = g_tuned.find(dev);
     if (it != g_tuned.end()) return small_units ? it->second.first : it->second.second;
-    int best = 101, best256 = 45;
+    int best = 101, best256 = 90;
     if (const char* env = getenv("NBODY_LARGE_VARIANT")) {
         const int id = atoi(env);
         if (find_variant(id) && !find_variant(id)->small) { g_tuned[dev] = std::make_pair(id, id); g_tune_report = "forced by NBODY_LARGE_VARIANT"; return id; }
@@ -532,7 +535,7 @@ int nbody_variant_info(int id, char* buf, size_t buflen)
         if (v->small) snprintf(cl, sizeof cl, ", small-N family: %d targets/CTA, sources split over the CTA, warp-shuffle reduction", v->T);
         snprintf(buf, buflen, "%s: %d targets/thread, %d threads/CTA, %d sources/tile, unroll %d pairs, %s FP32, min %d CTAs/SM, %zu B smem%s",
                  v->name, v->T, v->NT, v->UJ, v->unroll,
-                 v->packed == 0 ? "scalar" : v->packed == 1 ? "packed f32x2" : v->packed == 5 ? "packed f32x2, targets reversed" : v->packed == 6 ? "packed f32x2, target-outer order" : "packed f32x2, z-first order",
+                 v->packed == 0 ? "scalar" : v->packed == 1 ? "packed f32x2" : v->packed == 5 ? "packed f32x2, targets reversed" : v->packed == 6 ? "packed f32x2, target-outer order" : v->packed == 18 ? "packed f32x2, x,z,y order" : "packed f32x2, z-first order",
                  v->minb, v->smem(), cl);
     }
     return kNumVariants;

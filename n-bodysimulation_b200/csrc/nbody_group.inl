@@ -67,6 +67,15 @@ int load_nccl()
     return NBODY_OK;
 }
 
+// the group calls visit every device; the caller's current device is put back when they return
+struct DeviceRestore {
+    int dev = -1;
+    DeviceRestore() { if (cudaGetDevice(&dev) != cudaSuccess) dev = -1; }
+    ~DeviceRestore() { if (dev >= 0) cudaSetDevice(dev); }
+    DeviceRestore(const DeviceRestore&) = delete;
+    DeviceRestore& operator=(const DeviceRestore&) = delete;
+};
+
 #define NC(call)                                                                                   \
     do {                                                                                           \
         ncclResult_t r_ = (call);                                                                  \
@@ -75,6 +84,7 @@ int load_nccl()
 
 void group_destroy(nbody_ctx* c)
 {
+    DeviceRestore restore_;
     Group* g = c->group;
     if (g) {
         for (size_t i = 0; i < c->kids.size(); ++i) {
@@ -175,6 +185,7 @@ int group_create(nbody_ctx** out, const nbody_params* p)
 
 int group_sync(nbody_ctx* c)
 {
+    DeviceRestore restore_;
     Group* g = c->group;
     for (int d = 0; d < g->G; ++d) {
         int rc = set_device(c->kids[d]);
@@ -187,6 +198,7 @@ int group_sync(nbody_ctx* c)
 
 int group_upload(nbody_ctx* c, const float* x4, const float* v4)
 {
+    DeviceRestore restore_;
     // both source buffers of every device are rewritten: nobody may still be reading or storing into them
     int rc = group_sync(c);
     for (int d = 0; d < c->group->G && !rc; ++d) rc = upload_enqueue(c->kids[d], x4, v4);
@@ -197,6 +209,7 @@ int group_upload(nbody_ctx* c, const float* x4, const float* v4)
 
 int group_download(nbody_ctx* c, float* x4, float* v4, float* a4)
 {
+    DeviceRestore restore_;
     int rc = NBODY_OK;
     for (int d = 0; d < c->group->G && !rc; ++d) {
         nbody_ctx* k = c->kids[d];
@@ -209,6 +222,7 @@ int group_download(nbody_ctx* c, float* x4, float* v4, float* a4)
 
 int group_step_async(nbody_ctx* c, int nsteps)
 {
+    DeviceRestore restore_;
     Group* g = c->group;
     const int G = g->G;
     int rc = NBODY_OK;
@@ -279,6 +293,7 @@ int group_step_async(nbody_ctx* c, int nsteps)
 
 int group_elapsed_ms(nbody_ctx* c, float* ms)
 {
+    DeviceRestore restore_;
     Group* g = c->group;
     if (!g->timed) return fail(NBODY_E_STATE, "no timed call yet");
     float worst = 0.f;
@@ -317,6 +332,7 @@ int group_gather_state(nbody_ctx* c, bool with_v)
 
 int group_energy(nbody_ctx* c, double* ke, double* pe)
 {
+    DeviceRestore restore_;
     int rc = group_gather_state(c, true);
     if (rc) return rc;
     const double eps2 = c->p.integrator == NBODY_INTEG_F64 ? c->p.eps2_f64 : (double)c->p.eps2;
@@ -325,6 +341,7 @@ int group_energy(nbody_ctx* c, double* ke, double* pe)
 
 int group_render(nbody_ctx* c, const nbody_view* v, unsigned char* h_rgba)
 {
+    DeviceRestore restore_;
     int rc = group_gather_state(c, false);
     if (rc) return rc;
     return render_arrays(c->kids[0], c->group->Xfull, c->n, v, h_rgba);
@@ -332,6 +349,7 @@ int group_render(nbody_ctx* c, const nbody_view* v, unsigned char* h_rgba)
 
 int group_barrier_timeouts(nbody_ctx* c, int* timed_out)
 {
+    DeviceRestore restore_;
     int total = 0;
     for (nbody_ctx* k : c->kids) {
         int t = 0;
@@ -345,6 +363,7 @@ int group_barrier_timeouts(nbody_ctx* c, int* timed_out)
 
 int group_barrier_wait_ns(nbody_ctx* c, unsigned long long* total_ns, unsigned long long* max_ns, unsigned long long* waits, int reset)
 {
+    DeviceRestore restore_;
     unsigned long long bt = 0, bm = 0, bw = 0;
     for (nbody_ctx* k : c->kids) {
         unsigned long long t = 0, m = 0, w = 0;

@@ -24,6 +24,13 @@ namespace nbody {
 constexpr int kStages = 4;           // shared-memory ring depth
 constexpr int kLookahead = kStages - 2;  // tiles in flight ahead of the consumers
 constexpr int kMaxPeers = 15;        // other GPUs a context can store to (one NVSwitch domain)
+#ifndef NBODY_FOLD_UNITS
+#define NBODY_FOLD_UNITS 8           // 0: single-level summation (the round-1 kernel; `make sweep` evidence builds)
+#endif
+constexpr int kFoldEvery = NBODY_FOLD_UNITS;   // source units per first-level sum of force_kernel (see FOLD there)
+constexpr bool kFoldUnits = kFoldEvery != 0;
+// bytes of the per-thread totals behind the ring (+ barriers, flag, j-split scratch) of a force_kernel CTA
+__host__ __device__ constexpr size_t fold_bytes(int T, int NT, bool packed) { return packed && kFoldUnits ? (size_t)3 * T * NT * sizeof(float) : 0; }
 
 struct ForceArgs {
     // owned targets, AoS float4, indexed 0..n_targets (caller-visible layout)
@@ -156,8 +163,8 @@ __device__ __forceinline__ void integrate_one(const ForceArgs& a, int gi, bool v
 // worker that owns linear unit u when U units are cut into W equal ranges
 __device__ __forceinline__ int unit_owner(u64 u, u64 U, u64 W) { return (int)(((u + 1) * W - 1) / U); }
 
-// MODE: 0 scalar FFMA | 1 packed FADD2/FMUL2/FFMA2 | 5, 6, 7, 8 packed, the same arithmetic in another source
-//       order (5 targets reversed, 6 target-outer, 7 z first, 8 both 5 and 7): every target's sums are formed by
+// MODE: 0 scalar FFMA | 1 packed FADD2/FMUL2/FFMA2 | 5, 6, 7, 8, 18 packed, the same arithmetic in another source
+//       order (5 targets reversed, 6 target-outer, 7 z first, 8 both 5 and 7, 18 x,z,y): every target's sums are formed by
 //       the same operations in the same order, so the results are bit-identical; only ptxas' register
 //       allocation differs (worth a few per cent, see tuned_large_variant in nbody_engine.cu).
 // CS / CMODE: thread-block clusters (launch attribute clusterDim = CS).
@@ -172,12 +179,24 @@ template <int T, int NT, int UJ, int UNROLL, int MODE, int MINB, int CS = 1, int
 __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
 {
     constexpr bool PACKED = MODE != 0;
+    // Two-level summation: the packed accumulators cover kFoldEvery source units (4 096 bodies with 512-body units)
+    // and are then folded into per-thread scalar totals.  A target with one dominant neighbour otherwise adds ~N small
+    // terms to a large accumulator one by one, each rounded at the big term's ulp: measured at N = 1 M, uniform cube,
+    // that cost the worst bodies 1.7e-3 of their acceleration (the reference's own sequential fp32 sum: 3.3e-3) and
+    // 2e-4 on 64 sampled targets; folded, the big accumulator sees N / 4 096 additions and the same samples sit 1.3e-6
+    // from the fp64 sum.  The totals live in shared memory, one private column per thread ([3 T][NT] floats behind
+    // the ring): in registers they are 18 more live values across the inner loop.  Cost (profiles/r2_fold_sweep.txt):
+    // the fold itself is < 0.1 % of a unit's work, but ptxas schedules the inner loop around it differently --
+    // 2 738 G/s without, 2 645 .. 2 710 with, depending only on the source order of the three accumulations
+    // (x,z,y and z,y,x orders: 2 700 - 2 710; x,y,z: 2 645), hence the orders the dispatch table keeps.
+    constexpr bool FOLD = PACKED && kFoldUnits;
     constexpr bool MCAST = CS > 1 && CMODE == 1;
     constexpr bool JSPLIT = CS > 1 && CMODE == 2;
     constexpr int TI = T * NT;
     constexpr int TS = MCAST ? TI * CS : TI;   // targets of one worker's tile
     constexpr uint32_t kStageBytes = UJ * 16;
     static_assert((kStages & (kStages - 1)) == 0, "ring depth must be a power of two");
+    static_assert((kFoldEvery & (kFoldEvery - 1)) == 0, "fold group must be a power of two (or 0 = off)");
     static_assert((UJ / 2) % UNROLL == 0, "unroll must divide the pairs per unit");
     static_assert(CS == 1 || CMODE == 1 || CMODE == 2, "cluster variants need a mode");
     static_assert(!MCAST || (kStageBytes / CS) % 16 == 0, "multicast slices must be 16-byte multiples");
@@ -188,6 +207,7 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
     const uint32_t bar_empty = bar_full + 8 * kStages;
     volatile int* s_flag = reinterpret_cast<volatile int*>(smem_raw + kStages * kStageBytes + 16 * kStages);
     float4* s_red = reinterpret_cast<float4*>(smem_raw + kStages * kStageBytes + 16 * kStages + 16);   // JSPLIT only: [TI]
+    float* s_tot = reinterpret_cast<float*>(smem_raw + kStages * kStageBytes + 16 * kStages + 16 + (JSPLIT ? TI * 16 : 0)) + threadIdx.x;   // FOLD only: [3 T][NT]
 
     const int tid = threadIdx.x, lane = tid & 31;
     if (a.clk && blockIdx.x == 0 && tid == 0) { a.clk[0] = clock64(); a.clk[1] = globaltimer_ns(); }
@@ -283,6 +303,7 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
         // ---- targets into registers (negated: dx = xj + (-xi) is one FADD2) ----------
         u64 nx[T], ny[T], nz[T], ax[T], ay[T], az[T];
         float sx[T], sy[T], sz[T], qx[T], qy[T], qz[T];   // scalar variant
+
 #pragma unroll
         for (int t = 0; t < T; ++t) {
             const int gi = (MCAST ? it * CS + (int)crank : it) * TI + tid + t * NT;
@@ -295,11 +316,24 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
                 sx[t] = xi.x; sy[t] = xi.y; sz[t] = xi.z;
                 qx[t] = 0.f; qy[t] = 0.f; qz[t] = 0.f;
             }
+            if (FOLD) { s_tot[(3 * t) * NT] = 0.f; s_tot[(3 * t + 1) * NT] = 0.f; s_tot[(3 * t + 2) * NT] = 0.f; }
         }
 
         // ---- stream the source units of this segment ------------------------------------
+        // FOLD: groups of kFoldEvery units, each summed from zero in the packed accumulators and then folded into the
+        // totals -- a loop nest (group { zero; unit { pairs } ; fold }) rather than a conditional inside the unit
+        // loop, so that the unit loop keeps the shape ptxas schedules best (the same as without folding).
+        constexpr int JSTEP = JSPLIT ? CS : 1;
+        int jj = JSPLIT ? (int)crank : 0;
 #pragma unroll 1
-        for (int jj = JSPLIT ? (int)crank : 0; jj < jn; jj += JSPLIT ? CS : 1, ++k) {
+        while (jj < jn) {
+        const int jg_end = FOLD ? (jj + kFoldEvery * JSTEP < jn ? jj + kFoldEvery * JSTEP : jn) : jn;
+        if (FOLD) {
+#pragma unroll
+            for (int t = 0; t < T; ++t) { ax[t] = 0ull; ay[t] = 0ull; az[t] = 0ull; }
+        }
+#pragma unroll 1
+        for (; jj < jg_end; jj += JSTEP, ++k) {
             if (tid == 0) issue();
             const int s = k & (kStages - 1);
             mbar_wait(bar_full + 8 * s, (k / kStages) & 1);
@@ -308,9 +342,15 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
             auto interact2 = [&](const ulonglong2 xy, const ulonglong2 zm) {
 #pragma unroll
                 for (int tt = 0; tt < T; ++tt) {
-                    const int t = (MODE == 5 || MODE == 8) ? T - 1 - tt : tt;   // MODE 5/8: same arithmetic, targets visited in reverse
+                    // source order only (same operations, same order inside every sum): REV targets back to front;
+                    // order of the three differences (DORD) and of the three accumulations (AORD): 0 xyz, 1 zyx, 5 xzy
+                    constexpr bool REV = MODE == 5 || MODE == 8;
+                    constexpr int DORD = (MODE == 7 || MODE == 8) ? 1 : MODE == 18 ? 5 : 0;
+                    constexpr int AORD = DORD;
+                    const int t = REV ? T - 1 - tt : tt;
                     u64 dx, dy, dz;
-                    if (MODE == 7 || MODE == 8) { dz = add2(zm.x, nz[t]); dy = add2(xy.y, ny[t]); dx = add2(xy.x, nx[t]); }   // z first
+                    if (DORD == 1) { dz = add2(zm.x, nz[t]); dy = add2(xy.y, ny[t]); dx = add2(xy.x, nx[t]); }
+                    else if (DORD == 5) { dx = add2(xy.x, nx[t]); dz = add2(zm.x, nz[t]); dy = add2(xy.y, ny[t]); }
                     else { dx = add2(xy.x, nx[t]); dy = add2(xy.y, ny[t]); dz = add2(zm.x, nz[t]); }
                     u64 r2 = fma2(dx, dx, eps2p);
                     r2 = fma2(dy, dy, r2);
@@ -319,7 +359,8 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
                     float lo, hi;
                     unpack2(d3, lo, hi);
                     const u64 sc = mul2(pack2(rsqrt_mufu(lo), rsqrt_mufu(hi)), zm.y);
-                    if (MODE == 7 || MODE == 8) { az[t] = fma2(dz, sc, az[t]); ay[t] = fma2(dy, sc, ay[t]); ax[t] = fma2(dx, sc, ax[t]); }
+                    if (AORD == 1) { az[t] = fma2(dz, sc, az[t]); ay[t] = fma2(dy, sc, ay[t]); ax[t] = fma2(dx, sc, ax[t]); }
+                    else if (AORD == 5) { ax[t] = fma2(dx, sc, ax[t]); az[t] = fma2(dz, sc, az[t]); ay[t] = fma2(dy, sc, ay[t]); }
                     else { ax[t] = fma2(dx, sc, ax[t]); ay[t] = fma2(dy, sc, ay[t]); az[t] = fma2(dz, sc, az[t]); }
                 }
             };
@@ -385,12 +426,24 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
                 mbar_arrive(bar_empty + 8 * s);
             }
         }
+        if (FOLD) {   // this group's sums into the totals
+#pragma unroll
+            for (int t = 0; t < T; ++t) {
+                float lo, hi;
+                unpack2(ax[t], lo, hi); s_tot[(3 * t) * NT] = __fadd_rn(s_tot[(3 * t) * NT], __fadd_rn(lo, hi));
+                unpack2(ay[t], lo, hi); s_tot[(3 * t + 1) * NT] = __fadd_rn(s_tot[(3 * t + 1) * NT], __fadd_rn(lo, hi));
+                unpack2(az[t], lo, hi); s_tot[(3 * t + 2) * NT] = __fadd_rn(s_tot[(3 * t + 2) * NT], __fadd_rn(lo, hi));
+            }
+        }
+        }
 
         // ---- segment done: fused epilogue, or split-tile fix-up ------------------------
         float fx[T], fy[T], fz[T];
 #pragma unroll
         for (int t = 0; t < T; ++t) {
-            if (PACKED) {
+            if (FOLD) {
+                fx[t] = s_tot[(3 * t) * NT]; fy[t] = s_tot[(3 * t + 1) * NT]; fz[t] = s_tot[(3 * t + 2) * NT];
+            } else if (PACKED) {
                 float lo, hi;
                 unpack2(ax[t], lo, hi); fx[t] = lo + hi;
                 unpack2(ay[t], lo, hi); fy[t] = lo + hi;
