@@ -19,24 +19,31 @@ for p in (ROOT, os.path.join(ROOT, "oracle")):
 import nbody_b200 as nb  # noqa: E402
 import oracle as o       # noqa: E402
 
+o.set_num_threads()
+
 
 def rate(n, ms):
     return round(n * float(n) / ms / 1e6, 1)
 
 
 def lockstep(n, steps, x0, v0=None, dt=0.1):
-    """engine and O2 advanced side by side; error of the engine's state against O2's after every step"""
+    """engine and O2 advanced side by side; error of the engine's state against O2's after every step, and of each
+    one's acceleration against the fp64 sum over ITS OWN positions at the step's start (so the two columns
+    err_a_vs_fp64 / reference_fp32_err_vs_fp64 say how far each arithmetic is from exact, per step)"""
     X, V, A = x0.copy(), (np.zeros_like(x0) if v0 is None else v0.copy()), np.zeros_like(x0)
     rows, ms_total = [], 0.0
     with nb.Simulation(n, dt=dt) as sim:
         sim.upload(x0, v0)
         name = sim.info()["variant_name"]
+        x = x0
         for s in range(steps):
+            a64_ours, a64_ref = o.accel_f64(np.ascontiguousarray(x)), o.accel_f64(X)
             sim.step(1)
             ms_total += sim.elapsed_ms()
             o.step_snapshot(X, A, V, dt=dt)
             x, v, a = sim.download()
             rows.append({"step": s + 1, "err_a": o.norm_rel_err(a, A), "err_x": o.norm_rel_err(x, X), "err_v": o.norm_rel_err(v, V),
+                         "err_a_vs_fp64": o.norm_rel_err(a, a64_ours), "reference_fp32_err_vs_fp64": o.norm_rel_err(A, a64_ref),
                          "reference_1pct_test_failures_x": int(o.verify_still_bodies(x, X))})
     return name, rows, ms_total / steps
 
@@ -65,7 +72,9 @@ def main():
     out["configs"].append({"config": 2, "n": n, "ic": "uniform seed 12345", "kernel": name, "steps": rows,
                            "err_a_vs_fp64_step1": e_ours, "reference_fp32_err_vs_fp64_step1": e_ref,
                            "ms_per_step_single_launches": round(ms, 4), "g_inter_per_s": rate(n, ms),
-                           "ok": bool(e_ours <= max(1e-5, 1.5 * e_ref))})
+                           "tolerance": "north_star asks <= 1e-5 vs validation.cpp after one step; at this N the reference's own fp32 sum is that far from "
+                                        "the fp64 sum itself, so the bound is stated against fp64: err_a_vs_fp64 <= max(1e-5, 1.5 x reference_fp32_err_vs_fp64), every step",
+                           "ok": bool(e_ours <= max(1e-5, 1.5 * e_ref) and all(r["err_a_vs_fp64"] <= max(1e-5, 1.5 * r["reference_fp32_err_vs_fp64"]) for r in rows))})
 
     # config 3: N = 131072 Plummer, 100 steps, effective-energy drift (E_eff = KE + PE/2)
     n = 131072
