@@ -641,6 +641,7 @@ def run_ours(args):
     # ---- mid sizes on one GPU (BASELINE configs[1], [2]) -----------------------------------------------
     small_n = None
     ref_gpu = None
+    single_level = None
     if rank == 0 and not args.no_extras:
         if world == 1:
             small_n = []
@@ -652,6 +653,22 @@ def run_ours(args):
                     small_n.append({"n_bodies": nn, "steps": st, "us_per_step": round(ms * 1e3, 2), "value": round(nn * float(nn) / ms / 1e6, 1),
                                     "pct_fp32_peak": round(100 * FLOP_PER_INTERACTION * nn * float(nn) / ms / 1e9 / peak_tflops, 2),
                                     "kernel": s.info()["variant_name"], "timing": "nbody_step(ctx, steps), one CUDA-event pair around the loop"})
+        if world == 1:   # the same kernel with ONE running sum per target (nbody_params.summation = NBODY_SUM_SINGLE): speed vs accuracy
+            import numpy as np
+            o = _oracle()
+            xs = nb.ic_uniform(n, seed=12345)
+            idx = np.random.default_rng(3).choice(n, 128, replace=False).astype(np.int32)
+            a64 = o.accel_f64(xs, idx)
+            single_level = {}
+            for name, mode in (("two_level (default)", nb.NBODY_SUM_TWO_LEVEL), ("single_level", nb.NBODY_SUM_SINGLE)):
+                with nb.Simulation(n, device=local, summation=mode) as s:
+                    s.upload(xs).step(1)
+                    a1 = s.download()[2]
+                    s.step(3)
+                    ms = s.elapsed_ms() / 3
+                single_level[name] = {"value": round(n * float(n) / ms / 1e6, 1), "ms_per_step": round(ms, 3),
+                                      "err_a_vs_fp64_128_targets": float(norm_rel(a1[idx], a64).max())}
+            single_level["reference_fp32_err_vs_fp64"] = float(norm_rel(o.accel_f32(xs, idx), a64).max())
         try:   # B2: the reference's own kernel.cu rebuilt for sm_100, through its own simulate(); reported baseline
             ref_kernel_rate("libref_kernel_sm100.so", 16384, 1, 1)
             r = ref_kernel_rate("libref_kernel_sm100.so", 1 << 20, 1, 0)
@@ -704,6 +721,8 @@ def run_ours(args):
             line["series"] = series
         if small_n is not None:
             line["small_n"] = small_n
+        if single_level is not None:
+            line["summation"] = single_level
         if ref_gpu is not None:
             line["ref_gpu_baseline"] = ref_gpu
         if capi is not None:

@@ -37,6 +37,13 @@ extern "C" {
 #define NBODY_INTEG_MIXED 2   /* TestProject/kernel.cu:455-463 (reduction flavours):      */
                               /* `0.5 * DT * a` in double, drift `DT * v` in float (FMA)  */
 
+/* summation of a target's N pair terms in the large-N kernels */
+#define NBODY_SUM_TWO_LEVEL 0 /* groups of 8 source units (4 096 bodies) summed from zero, then added to a total: */
+                              /* 7.7e-7 from the fp64 sum at N = 1 M where one running fp32 sum is at 6.6e-5  */
+                              /* and the reference's own sequential sum at 2.6e-4       */
+#define NBODY_SUM_SINGLE    1 /* one running sum per target and lane, as the reference's kernel.cu:55-65 has: */
+                              /* 2 % faster (ptxas schedules the inner loop better), ~100 x less accurate     */
+
 /* kernel variant: 0 = choose from N; others are listed by nbody_variant_info() */
 #define NBODY_VARIANT_AUTO 0
 
@@ -77,6 +84,7 @@ typedef struct nbody_params {
                          /*    Needs rank 0, world 1.  0 or 1: the single `device` above [0]  */
     int   exchange;      /* NBODY_EXCHANGE_P2P | _NCCL | _P2P_EVENTS (n_devices > 1)  [P2P]   */
     int   devices[NBODY_MAX_DEVICES];   /* CUDA ordinals, all different (see _P2P_EVENTS)     */
+    int   summation;     /* NBODY_SUM_TWO_LEVEL | NBODY_SUM_SINGLE                    [TWO_LEVEL] */
 } nbody_params;
 
 /* Fills *p with the defaults listed above (TestProject/constants.h). */

@@ -32,6 +32,7 @@ lib = C.CDLL(LIB_PATH)
 NBODY_INTEG_F32, NBODY_INTEG_F64, NBODY_INTEG_MIXED = 0, 1, 2
 NBODY_EXCHANGE_P2P, NBODY_EXCHANGE_NCCL, NBODY_EXCHANGE_P2P_EVENTS = 0, 1, 2
 NBODY_MAX_DEVICES = 16
+NBODY_SUM_TWO_LEVEL, NBODY_SUM_SINGLE = 0, 1
 
 
 class NBodyParams(C.Structure):
@@ -41,7 +42,7 @@ class NBodyParams(C.Structure):
                 ("device", C.c_int), ("variant", C.c_int), ("grid_ctas", C.c_int),
                 ("eps2_f64", C.c_double), ("dt_f64", C.c_double),
                 ("deterministic", C.c_int), ("n_devices", C.c_int), ("exchange", C.c_int),
-                ("devices", C.c_int * NBODY_MAX_DEVICES)]
+                ("devices", C.c_int * NBODY_MAX_DEVICES), ("summation", C.c_int)]
 
 
 class NBodyStepOpts(C.Structure):
@@ -262,7 +263,7 @@ class Simulation:
     def __init__(self, n: int, eps2: float = 0.002, dt: float = 0.1, *, rank: int = 0, world: int = 1,
                  device: int = 0, variant: int = 0, grid_ctas: int = 0, integrator: int = NBODY_INTEG_F32,
                  eps2_f64: float = 0.002, dt_f64: float = 0.01, devices=None, exchange: int = NBODY_EXCHANGE_P2P,
-                 deterministic: bool = False):
+                 deterministic: bool = False, summation: int = NBODY_SUM_TWO_LEVEL):
         """devices=[d0, d1, ...]: ONE context spanning those GPUs (nbody_params.n_devices): the same upload / step /
         download / energy / save calls then drive the whole box from this thread."""
         p = NBodyParams()
@@ -270,7 +271,7 @@ class Simulation:
         p.n_bodies, p.rank, p.world, p.eps2, p.dt = n, rank, world, eps2, dt
         p.device, p.variant, p.grid_ctas, p.integrator = device, variant, grid_ctas, integrator
         p.eps2_f64, p.dt_f64 = eps2_f64, dt_f64
-        p.deterministic, p.exchange = int(deterministic), exchange
+        p.deterministic, p.exchange, p.summation = int(deterministic), exchange, summation
         if devices is not None and len(devices) > 1:
             assert len(devices) <= NBODY_MAX_DEVICES
             p.n_devices = len(devices)

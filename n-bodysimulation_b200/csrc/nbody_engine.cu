@@ -63,19 +63,21 @@ struct Variant {
     int T, NT, UJ, unroll, packed, minb;
     int cs, cmode;   // cluster size (1 = none); 1 = TMA multicast of source units, 2 = j-split + DSMEM reduction
     void (*kernel)(const ForceArgs);
+    void (*kernel_single)(const ForceArgs);   // the same kernel with single-level summation (null: small-N family)
     int small = 0;   // 1: small_kernel (T = targets per CTA, sources split over the CTA's threads, shuffle reduction)
-    size_t smem() const { return small ? 0 : (size_t)kStages * UJ * 16 + 16 * kStages + 16 + (cmode == 2 ? (size_t)TI() * 16 : 0) + fold_bytes(T, NT, packed != 0); }
+    size_t smem(bool single = false) const { return small ? 0 : (size_t)kStages * UJ * 16 + 16 * kStages + 16 + (cmode == 2 ? (size_t)TI() * 16 : 0) + fold_bytes(T, NT, packed != 0, !single); }
+    void (*entry(bool single) const)(const ForceArgs) { return single && kernel_single ? kernel_single : kernel; }
     int TI() const { return small ? T : T * NT; }
     int TS() const { return cmode == 1 ? TI() * cs : TI(); }          // targets per worker tile
 };
 
 #define VARIANT(id, T, NT, UJ, UN, PK, MB) \
-    { id, "T" #T "_NT" #NT "_UJ" #UJ "_U" #UN "_" #PK "_B" #MB, T, NT, UJ, UN, PK, MB, 1, 0, force_kernel<T, NT, UJ, UN, PK, MB> }
+    { id, "T" #T "_NT" #NT "_UJ" #UJ "_U" #UN "_" #PK "_B" #MB, T, NT, UJ, UN, PK, MB, 1, 0, force_kernel<T, NT, UJ, UN, PK, MB>, force_kernel<T, NT, UJ, UN, PK, MB, 1, 0, 0> }
 #define CVARIANT(id, T, NT, UJ, UN, PK, MB, CS, CM) \
-    { id, "T" #T "_NT" #NT "_UJ" #UJ "_U" #UN "_" #PK "_B" #MB "_C" #CS "m" #CM, T, NT, UJ, UN, PK, MB, CS, CM, force_kernel<T, NT, UJ, UN, PK, MB, CS, CM> }
+    { id, "T" #T "_NT" #NT "_UJ" #UJ "_U" #UN "_" #PK "_B" #MB "_C" #CS "m" #CM, T, NT, UJ, UN, PK, MB, CS, CM, force_kernel<T, NT, UJ, UN, PK, MB, CS, CM>, force_kernel<T, NT, UJ, UN, PK, MB, CS, CM, 0> }
 
 #define SVARIANT(id, TT, NT, UN) \
-    { id, "S_TT" #TT "_NT" #NT "_U" #UN, TT, NT, 64, UN, 1, 1, 1, 0, small_kernel<TT, NT, UN>, 1 }
+    { id, "S_TT" #TT "_NT" #NT "_U" #UN, TT, NT, 64, UN, 1, 1, 1, 0, small_kernel<TT, NT, UN>, nullptr, 1 }
 // packed: 0 = scalar FFMA path (kept as the with/without evidence of the f32x2 choice), 1 = FADD2/FMUL2/FFMA2,
 // 5 / 6 / 7 / 8 = the same packed arithmetic in another source order (bit-identical results; ptxas' register
 // allocation differs by a few per cent, see tuned_large_variant).
@@ -113,6 +115,7 @@ const Variant kVariants[] = {
     VARIANT(106, 6, 256, 512, 2, 1, 1),
     VARIANT(107, 6, 256, 512, 2, 5, 1),
     VARIANT(129, 6, 256, 1024, 2, 7, 1),
+    VARIANT(140, 6, 256, 512, 2, 19, 1),     // scalar FMUL behind each MUFU.RSQ (experiment, profiles/r2_scalar_tail_experiment.txt)
     VARIANT(1, 4, 256, 256, 4, 1, 2),
     VARIANT(2, 2, 256, 256, 4, 1, 4),
     VARIANT(4, 4, 128, 256, 4, 1, 4),
@@ -236,11 +239,13 @@ bool eps2_representable(float eps2)
 struct Plan {
     int grid = 0, occ = 0, maxseg = 0, num_itiles = 0, num_counters = 0;
     size_t partial_bytes = 0;
+    bool single = false;   // single-level summation kernel (nbody_params.summation)
 };
 
-int make_plan(const Variant* v, int sm_count, int grid_override, int n_targets, int J, Plan* out)
+int make_plan(const Variant* v, int sm_count, int grid_override, int n_targets, int J, Plan* out, bool single = false)
 {
     Plan pl;
+    pl.single = single && v->kernel_single;
     if (v->small) {   // one CTA per T targets, every CTA visits all J units: nothing to cut, no scratch
         (void)sm_count; (void)grid_override; (void)J;
         pl.occ = 1;
@@ -250,8 +255,8 @@ int make_plan(const Variant* v, int sm_count, int grid_override, int n_targets, 
         *out = pl;
         return NBODY_OK;
     }
-    CU(cudaFuncSetAttribute(v->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v->smem()));
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pl.occ, v->kernel, v->NT, v->smem()));
+    CU(cudaFuncSetAttribute(v->entry(pl.single), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v->smem(pl.single)));
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pl.occ, v->entry(pl.single), v->NT, v->smem(pl.single)));
     if (pl.occ < 1) return fail(NBODY_E_CUDA, "variant %s does not fit on an SM", v->name);
     long long workers = (long long)sm_count * pl.occ;   // CTAs, or clusters for the cluster variants
     if (v->cs > 1) {
@@ -260,9 +265,9 @@ int make_plan(const Variant* v, int sm_count, int grid_override, int n_targets, 
         at[0].id = cudaLaunchAttributeClusterDimension;
         at[0].val.clusterDim.x = v->cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
         cfg.gridDim = dim3((unsigned)(sm_count * pl.occ / v->cs * v->cs)); cfg.blockDim = dim3(v->NT);
-        cfg.dynamicSmemBytes = v->smem(); cfg.attrs = at; cfg.numAttrs = 1;
+        cfg.dynamicSmemBytes = v->smem(pl.single); cfg.attrs = at; cfg.numAttrs = 1;
         int ncl = 0;
-        CU(cudaOccupancyMaxActiveClusters(&ncl, v->kernel, &cfg));
+        CU(cudaOccupancyMaxActiveClusters(&ncl, v->entry(pl.single), &cfg));
         if (ncl < 1) return fail(NBODY_E_CUDA, "no cluster of %d CTAs of variant %s can be resident", v->cs, v->name);
         workers = ncl;
     }
@@ -288,11 +293,11 @@ int launch_force(const Variant* v, const Plan& pl, const ForceArgs& args_in, cud
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeClusterDimension;
         at[0].val.clusterDim.x = v->cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-        cfg.gridDim = dim3(pl.grid); cfg.blockDim = dim3(v->NT); cfg.dynamicSmemBytes = v->smem(); cfg.stream = st;
+        cfg.gridDim = dim3(pl.grid); cfg.blockDim = dim3(v->NT); cfg.dynamicSmemBytes = v->smem(pl.single); cfg.stream = st;
         cfg.attrs = at; cfg.numAttrs = 1;
-        CU(cudaLaunchKernelEx(&cfg, v->kernel, args));
+        CU(cudaLaunchKernelEx(&cfg, v->entry(pl.single), args));
     } else {
-        v->kernel<<<pl.grid, v->NT, v->smem(), st>>>(args);
+        v->entry(pl.single)<<<pl.grid, v->NT, v->smem(pl.single), st>>>(args);
     }
     g_launches.fetch_add(1, std::memory_order_relaxed);
     CU(cudaGetLastError());
@@ -470,13 +475,14 @@ int plan_scratch(nbody_ctx* c)
 {
     const int UJ = c->var->UJ;
     const int units_total = c->n_src_pad / UJ, units_own = c->slot_bodies / UJ;
-    int rc = make_plan(c->var, c->sm_count, c->p.grid_ctas, c->n_targets, units_total, &c->plan_full);
+    const bool single = c->p.summation == NBODY_SUM_SINGLE;
+    int rc = make_plan(c->var, c->sm_count, c->p.grid_ctas, c->n_targets, units_total, &c->plan_full, single);
     if (rc) return rc;
     size_t partial_bytes = c->plan_full.partial_bytes;
     if (c->p.world > 1) {
-        rc = make_plan(c->var, c->sm_count, c->p.grid_ctas, c->n_targets, units_own, &c->plan_local);
+        rc = make_plan(c->var, c->sm_count, c->p.grid_ctas, c->n_targets, units_own, &c->plan_local, single);
         if (rc) return rc;
-        rc = make_plan(c->var, c->sm_count, c->p.grid_ctas, c->n_targets, units_total - units_own, &c->plan_remote);
+        rc = make_plan(c->var, c->sm_count, c->p.grid_ctas, c->n_targets, units_total - units_own, &c->plan_remote, single);
         if (rc) return rc;
         if (c->plan_local.partial_bytes > partial_bytes) partial_bytes = c->plan_local.partial_bytes;
         if (c->plan_remote.partial_bytes > partial_bytes) partial_bytes = c->plan_remote.partial_bytes;
@@ -598,6 +604,7 @@ int nbody_create(nbody_ctx** out, const nbody_params* p)
     if (p->world < 1 || p->rank < 0 || p->rank >= p->world) return fail(NBODY_E_INVALID, "bad shard %d of %d", p->rank, p->world);
     const bool f64 = p->integrator == NBODY_INTEG_F64;
     if (!f64 && p->integrator != NBODY_INTEG_F32 && p->integrator != NBODY_INTEG_MIXED) return fail(NBODY_E_INVALID, "unknown integrator %d", p->integrator);
+    if (p->summation != NBODY_SUM_TWO_LEVEL && p->summation != NBODY_SUM_SINGLE) return fail(NBODY_E_INVALID, "unknown summation %d", p->summation);
     // the self term is 0 * m / eps2^1.5 and the zero-mass padding sits at the
     // origin: both need eps2 > 0 to stay finite
     if (!((f64 ? p->eps2_f64 : (double)p->eps2) > 0.0)) return fail(NBODY_E_INVALID, "eps2 must be > 0");

@@ -30,7 +30,7 @@ constexpr int kMaxPeers = 15;        // other GPUs a context can store to (one N
 constexpr int kFoldEvery = NBODY_FOLD_UNITS;   // source units per first-level sum of force_kernel (see FOLD there)
 constexpr bool kFoldUnits = kFoldEvery != 0;
 // bytes of the per-thread totals behind the ring (+ barriers, flag, j-split scratch) of a force_kernel CTA
-__host__ __device__ constexpr size_t fold_bytes(int T, int NT, bool packed) { return packed && kFoldUnits ? (size_t)3 * T * NT * sizeof(float) : 0; }
+__host__ __device__ constexpr size_t fold_bytes(int T, int NT, bool packed, bool two_level = true) { return packed && kFoldUnits && two_level ? (size_t)3 * T * NT * sizeof(float) : 0; }
 
 struct ForceArgs {
     // owned targets, AoS float4, indexed 0..n_targets (caller-visible layout)
@@ -175,7 +175,8 @@ __device__ __forceinline__ int unit_owner(u64 u, u64 U, u64 W) { return (int)(((
 //   CMODE 2 "j-split": the CS CTAs share ONE target tile and take every CS-th source unit of
 //           the segment; the partial sums are combined through distributed shared memory
 //           (ld.shared::cluster, fixed rank order), CTA r finishing slice r of the tile.
-template <int T, int NT, int UJ, int UNROLL, int MODE, int MINB, int CS = 1, int CMODE = 0>
+// FOLDK: source units per first-level sum (0 = single-level summation, nbody_params.summation = NBODY_SUM_SINGLE)
+template <int T, int NT, int UJ, int UNROLL, int MODE, int MINB, int CS = 1, int CMODE = 0, int FOLDK = kFoldEvery>
 __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
 {
     constexpr bool PACKED = MODE != 0;
@@ -189,14 +190,14 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
     // the fold itself is < 0.1 % of a unit's work, but ptxas schedules the inner loop around it differently --
     // 2 738 G/s without, 2 645 .. 2 710 with, depending only on the source order of the three accumulations
     // (x,z,y and z,y,x orders: 2 700 - 2 710; x,y,z: 2 645), hence the orders the dispatch table keeps.
-    constexpr bool FOLD = PACKED && kFoldUnits;
+    constexpr bool FOLD = PACKED && FOLDK != 0;
     constexpr bool MCAST = CS > 1 && CMODE == 1;
     constexpr bool JSPLIT = CS > 1 && CMODE == 2;
     constexpr int TI = T * NT;
     constexpr int TS = MCAST ? TI * CS : TI;   // targets of one worker's tile
     constexpr uint32_t kStageBytes = UJ * 16;
     static_assert((kStages & (kStages - 1)) == 0, "ring depth must be a power of two");
-    static_assert((kFoldEvery & (kFoldEvery - 1)) == 0, "fold group must be a power of two (or 0 = off)");
+    static_assert((FOLDK & (FOLDK - 1)) == 0, "fold group must be a power of two (or 0 = off)");
     static_assert((UJ / 2) % UNROLL == 0, "unroll must divide the pairs per unit");
     static_assert(CS == 1 || CMODE == 1 || CMODE == 2, "cluster variants need a mode");
     static_assert(!MCAST || (kStageBytes / CS) % 16 == 0, "multicast slices must be 16-byte multiples");
@@ -327,7 +328,7 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
         int jj = JSPLIT ? (int)crank : 0;
 #pragma unroll 1
         while (jj < jn) {
-        const int jg_end = FOLD ? (jj + kFoldEvery * JSTEP < jn ? jj + kFoldEvery * JSTEP : jn) : jn;
+        const int jg_end = FOLD ? (jj + FOLDK * JSTEP < jn ? jj + FOLDK * JSTEP : jn) : jn;
         if (FOLD) {
 #pragma unroll
             for (int t = 0; t < T; ++t) { ax[t] = 0ull; ay[t] = 0ull; az[t] = 0ull; }
@@ -345,7 +346,7 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
                     // source order only (same operations, same order inside every sum): REV targets back to front;
                     // order of the three differences (DORD) and of the three accumulations (AORD): 0 xyz, 1 zyx, 5 xzy
                     constexpr bool REV = MODE == 5 || MODE == 8;
-                    constexpr int DORD = (MODE == 7 || MODE == 8) ? 1 : MODE == 18 ? 5 : 0;
+                    constexpr int DORD = (MODE == 7 || MODE == 8 || MODE == 19) ? 1 : MODE == 18 ? 5 : 0;
                     constexpr int AORD = DORD;
                     const int t = REV ? T - 1 - tt : tt;
                     u64 dx, dy, dz;
@@ -358,7 +359,17 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
                     const u64 d3 = mul2(mul2(r2, r2), r2);      // (r^2+eps2)^3, as kernel.cu:20
                     float lo, hi;
                     unpack2(d3, lo, hi);
-                    const u64 sc = mul2(pack2(rsqrt_mufu(lo), rsqrt_mufu(hi)), zm.y);
+                    u64 sc;
+                    if (MODE == 19) {
+                        // experiment (DESIGN section 8, round 1 "untried"): the two m * r^-3 products as SCALAR FMULs, one
+                        // behind each MUFU.RSQ, so that a 1-cycle FP32 op rather than a 2-cycle packed one sits next to
+                        // the MUFU issue (which costs the FMA pipe 1.17 issue cycles, profiles/r1_microbench_pipes.jsonl)
+                        float mlo, mhi;
+                        unpack2(zm.y, mlo, mhi);
+                        sc = pack2(__fmul_rn(rsqrt_mufu(lo), mlo), __fmul_rn(rsqrt_mufu(hi), mhi));
+                    } else {
+                        sc = mul2(pack2(rsqrt_mufu(lo), rsqrt_mufu(hi)), zm.y);
+                    }
                     if (AORD == 1) { az[t] = fma2(dz, sc, az[t]); ay[t] = fma2(dy, sc, ay[t]); ax[t] = fma2(dx, sc, ax[t]); }
                     else if (AORD == 5) { ax[t] = fma2(dx, sc, ax[t]); az[t] = fma2(dz, sc, az[t]); ay[t] = fma2(dy, sc, ay[t]); }
                     else { ax[t] = fma2(dx, sc, ax[t]); ay[t] = fma2(dy, sc, ay[t]); az[t] = fma2(dz, sc, az[t]); }

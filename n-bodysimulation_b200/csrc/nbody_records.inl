@@ -69,7 +69,8 @@ int nbody_snapshot_save(nbody_ctx* c, const char* path)
     memcpy(h.magic, kSnapshotMagic, 8);
     h.version = 2; h.n = (unsigned)c->n; h.steps_done = (unsigned long long)c->steps_done;
     h.eps2 = c->p.eps2; h.dt = c->p.dt; h.integrator = c->p.integrator;
-    h.variant = c->kids.empty() ? (unsigned)c->var->id : 0u;
+    // low 16 bits: kernel variant; bit 16: single-level summation
+    h.variant = c->kids.empty() ? ((unsigned)c->var->id | (c->plan_full.single ? 0x10000u : 0u)) : 0u;
     h.eps2_f64 = c->p.eps2_f64; h.dt_f64 = c->p.dt_f64;
     h.checksum = fnv1a(v.data(), nb, fnv1a(x.data(), nb));
     FILE* f = fopen(path, "wb");
@@ -112,13 +113,15 @@ int nbody_snapshot_load(nbody_ctx* c, const char* path)
     if (h.version >= 2 && h.checksum != fnv1a(v.data(), nb, fnv1a(x.data(), nb)))
         return fail(NBODY_E_INVALID, "%s: payload checksum mismatch (corrupted file)", path);
     // bit-identical resume: run the kernel the saver ran (same tile shape and unit size = same summation order)
-    if (h.version >= 2 && h.variant != 0 && c->kids.empty() && c->p.world == 1 && (int)h.variant != c->var->id) {
-        const Variant* sv = find_variant((int)h.variant);
+    if (h.version >= 2 && h.variant != 0 && c->kids.empty() && c->p.world == 1 && ((h.variant & 0x10000u) != 0) != c->plan_full.single)
+        return fail(NBODY_E_STATE, "%s was written with %s summation, the context uses the other one (nbody_params.summation)", path, (h.variant & 0x10000u) ? "single-level" : "two-level");
+    if (h.version >= 2 && h.variant != 0 && c->kids.empty() && c->p.world == 1 && (int)(h.variant & 0xffffu) != c->var->id) {
+        const Variant* sv = find_variant((int)(h.variant & 0xffffu));
         const bool same_sums = sv && sv->small == c->var->small && sv->T == c->var->T && sv->NT == c->var->NT && sv->UJ == c->var->UJ && sv->cs == c->var->cs && sv->cmode == c->var->cmode;
         if (!same_sums) {
             if (c->p.variant != NBODY_VARIANT_AUTO)
-                return fail(NBODY_E_STATE, "%s was written by kernel variant %u; the context was created with variant %d (other summation order): create it with NBODY_VARIANT_AUTO or that variant", path, h.variant, c->p.variant);
-            if (!sv) return fail(NBODY_E_STATE, "%s was written by kernel variant %u, which this build of the library does not have", path, h.variant);
+                return fail(NBODY_E_STATE, "%s was written by kernel variant %u; the context was created with variant %d (other summation order): create it with NBODY_VARIANT_AUTO or that variant", path, h.variant & 0xffffu, c->p.variant);
+            if (!sv) return fail(NBODY_E_STATE, "%s was written by kernel variant %u, which this build of the library does not have", path, h.variant & 0xffffu);
             int rc = repin_variant(c, sv);
             if (rc) return rc;
         }

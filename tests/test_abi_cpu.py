@@ -44,7 +44,7 @@ def test_argument_validation(nb):
     h = C.c_void_p()
     p = nb.NBodyParams()
     nb.lib.nbody_params_default(C.byref(p))
-    for field, bad in (("n_bodies", 0), ("n_bodies", -5), ("eps2", 0.0), ("world", 0), ("rank", 3), ("integrator", 7)):
+    for field, bad in (("n_bodies", 0), ("n_bodies", -5), ("eps2", 0.0), ("world", 0), ("rank", 3), ("integrator", 7), ("summation", 7)):
         q = nb.NBodyParams.from_buffer_copy(p)
         setattr(q, field, bad)
         assert nb.lib.nbody_create(C.byref(h), C.byref(q)) == -1, field
@@ -70,7 +70,7 @@ def test_multi_device_parameters_are_validated_on_the_host(nb):
     h = C.c_void_p()
     p = nb.NBodyParams()
     nb.lib.nbody_params_default(C.byref(p))
-    assert (p.n_devices, p.exchange, p.deterministic) == (0, nb.NBODY_EXCHANGE_P2P, 0)
+    assert (p.n_devices, p.exchange, p.deterministic, p.summation) == (0, nb.NBODY_EXCHANGE_P2P, 0, nb.NBODY_SUM_TWO_LEVEL)
     q = nb.NBodyParams.from_buffer_copy(p)
     q.n_devices = nb.NBODY_MAX_DEVICES + 1
     assert nb.lib.nbody_create(C.byref(h), C.byref(q)) == -1

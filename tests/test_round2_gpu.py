@@ -130,6 +130,27 @@ def test_softening_at_the_accepted_lower_bound_stays_finite(cuda, nb, oracle):
         nb.Simulation(n, eps2=1e-13)
 
 
+def test_two_level_summation_is_closer_to_fp64_than_one_running_sum(cuda, nb, oracle, tmp_path):
+    # nbody_params.summation: the default folds groups of 8 source units into totals; NBODY_SUM_SINGLE keeps the
+    # round-1 kernel (one running fp32 sum per target and lane, as the reference has)
+    n = 300000
+    x0 = nb.ic_uniform(n, seed=31)
+    idx = np.random.default_rng(5).choice(n, 256, replace=False).astype(np.int32)
+    a64 = oracle.accel_f64(x0, idx)
+    ref = oracle.norm_rel_err(oracle.accel_f32(x0, idx), a64)
+    two = run_steps(nb, n, x0)
+    one = run_steps(nb, n, x0, summation=nb.NBODY_SUM_SINGLE)
+    e_two, e_one = oracle.norm_rel_err(two[2][idx], a64), oracle.norm_rel_err(one[2][idx], a64)
+    print(f"err vs fp64: two-level {e_two:.2e}, single-level {e_one:.2e}, reference fp32 {ref:.2e}")
+    assert e_two <= 5e-6 and e_two < e_one <= max(TOL_A, 2 * ref)
+    assert two[3] == one[3]                                      # same kernel variant, other summation
+    path = str(tmp_path / "s.nbody")
+    with nb.Simulation(n, summation=nb.NBODY_SUM_SINGLE) as sim:
+        sim.upload(x0).step(1).save(path)
+    with nb.Simulation(n) as sim, pytest.raises(nb.NBodyError, match="summation"):
+        sim.load(path)                                           # a resumed run would continue with other rounding
+
+
 # ---- ONE context over several devices (VERDICT r1 missing #2 / next #5) ---------------------------------------------
 def check_group(nb, oracle, n, devices, exchange, steps=3, tmp_path=None):
     x0, v0 = nb.ic_plummer(n, seed=3)
