@@ -80,6 +80,7 @@ def _worker(rank, world, port, n, steps, out_dir):
     runner = par.ShardedSimulation(sim, rank, world, device=None)
     for _ in range(steps):
         runner.step()
+    runner.quiesce()      # the fence bench.py puts around re-uploads: synchronise + cross-rank barrier (no streams on CPU)
     assert sim.calls == ["local", "remote"] * steps
     np.save(os.path.join(out_dir, f"x_{rank}.npy"), sim._all_bodies())       # everyone must hold all new positions
     np.save(os.path.join(out_dir, f"v_{rank}.npy"), sim.V)
