@@ -445,6 +445,13 @@ struct Cached {
     unsigned* counters = nullptr;
     float4 *X = nullptr, *V = nullptr, *A = nullptr;   // host-pointer flavour only
     int n_pad = 0;
+    // launch-bound sizes: pack + step kernel of ONE call as a two-node CUDA graph, re-used while the caller passes the
+    // same arrays and parameters (the reference's loop does, main.cpp:146-155): one graph launch instead of two
+    // kernel launches per simulate()
+    cudaGraphExec_t call_graph = nullptr;
+    cudaStream_t capture_stream = nullptr;
+    bool graph_failed = false;
+    struct CallKey { void *x, *a, *v; float eps2, dt; int integ, f3; double dt64; } key{};
 };
 void release_render_scratch();   // nbody_render.inl
 std::mutex g_cache_mu;
@@ -452,6 +459,8 @@ std::map<std::pair<std::pair<int, int>, int>, Cached> g_cache;   // ((device, N)
 
 void free_cached(Cached& k)
 {
+    if (k.call_graph) cudaGraphExecDestroy(k.call_graph);
+    if (k.capture_stream) cudaStreamDestroy(k.capture_stream);
     cudaFree(k.packed); cudaFree(k.partial); cudaFree(k.counters); cudaFree(k.X); cudaFree(k.V); cudaFree(k.A);
     k = Cached();
 }
@@ -485,10 +494,10 @@ int get_cached(int n, bool host_buffers, Cached** out, int variant = NBODY_VARIA
     return NBODY_OK;
 }
 
-int one_step_on_device(Cached* k, float4* dX, float4* dA, float4* dV, int n, float eps2, float dt, int f64, double dt64, int va_f3 = 0)
+int enqueue_one_step(Cached* k, float4* dX, float4* dA, float4* dV, int n, float eps2, float dt, int f64, double dt64, int va_f3, cudaStream_t st)
 {
     // snapshot of the step's start in packed form; X is then advanced in place
-    int rc = launch_pack(dX, n, k->packed, 0, k->n_pad, 0);
+    int rc = launch_pack(dX, n, k->packed, 0, k->n_pad, st);
     if (rc) return rc;
     ForceArgs a{};
     a.X = dX; a.V = dV; a.A = dA;
@@ -497,7 +506,40 @@ int one_step_on_device(Cached* k, float4* dX, float4* dA, float4* dV, int n, flo
     a.ra_begin = 0; a.ra_count = k->n_pad / k->var->UJ;
     a.partial = k->partial; a.counters = k->counters; a.maxseg = k->plan.maxseg;
     a.eps2 = eps2; a.dt = dt; a.integ_f64 = f64; a.dt64 = dt64; a.va_f3 = va_f3;
-    return launch_force(k->var, k->plan, a, 0);
+    return launch_force(k->var, k->plan, a, st);
+}
+
+int one_step_on_device(Cached* k, float4* dX, float4* dA, float4* dV, int n, float eps2, float dt, int f64, double dt64, int va_f3 = 0)
+{
+    if (n <= kGraphMaxBodies && !k->graph_failed) {
+        const Cached::CallKey key{dX, dA, dV, eps2, dt, f64, va_f3, dt64};
+        if (!k->call_graph || memcmp(&key, &k->key, sizeof key) != 0) {
+            if (k->call_graph) { cudaGraphExecDestroy(k->call_graph); k->call_graph = nullptr; }
+            cudaGraph_t g = nullptr;
+            bool ok = (k->capture_stream || cudaStreamCreateWithFlags(&k->capture_stream, cudaStreamNonBlocking) == cudaSuccess) &&
+                      cudaStreamBeginCapture(k->capture_stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+            if (ok) {
+                const bool enq = enqueue_one_step(k, dX, dA, dV, n, eps2, dt, f64, dt64, va_f3, k->capture_stream) == NBODY_OK;
+                ok = cudaStreamEndCapture(k->capture_stream, &g) == cudaSuccess && enq;
+                g_launches.fetch_sub(enq ? 2 : 0, std::memory_order_relaxed);   // nothing ran yet
+                ok = ok && cudaGraphInstantiate(&k->call_graph, g, 0) == cudaSuccess;
+                if (g) cudaGraphDestroy(g);
+            }
+            if (!ok) { cudaGetLastError(); k->call_graph = nullptr; k->graph_failed = true; }
+            else memcpy(&k->key, &key, sizeof key);
+        }
+        if (k->call_graph) {
+            if (cudaGraphLaunch(k->call_graph, 0) == cudaSuccess) {   // the caller's (legacy default) stream, like the reference's launch
+                g_launches.fetch_add(2, std::memory_order_relaxed);   // kernels run, not API calls
+                return NBODY_OK;
+            }
+            cudaGetLastError();   // not launchable here: plain launches from now on
+            cudaGraphExecDestroy(k->call_graph);
+            k->call_graph = nullptr;
+            k->graph_failed = true;
+        }
+    }
+    return enqueue_one_step(k, dX, dA, dV, n, eps2, dt, f64, dt64, va_f3, 0);
 }
 
 // ---- the in-place step spread over several GPUs (nbody_set_devices) --------------------------------------

@@ -1,6 +1,6 @@
 """sanitize_target.py -- small run of every kernel family for compute-sanitizer (one tool per gpurun call):
    compute-sanitizer --tool memcheck python tools/sanitize_target.py
-(compute-sanitizer is closed on this GPU pool in round 1; run plain, it is a 2-second pass over every family.)"""
+(compute-sanitizer answered "closed" on this GPU pool in round 1; run plain, it is a 2-second pass over every family.)"""
 import os
 import sys
 
@@ -12,8 +12,8 @@ import nbody_b200 as nb  # noqa: E402
 
 n = 1537                                   # ragged: not a multiple of any tile or unit
 x0 = nb.ic_uniform(n, seed=1)
-ids = [int(a) for a in sys.argv[1:]] or [12, 3, 45, 9, 17, 46, 91, 60, 61, 64, 65, 68, 82, 85]
-for vid in ids:                            # stream-K, scalar, prefetch modes, orderings, cluster multicast / DSMEM, small family
+ids = [int(a) for a in sys.argv[1:]] or [12, 3, 90, 97, 105, 9, 93, 111, 113, 60, 64, 82, 85]
+for vid in ids:                            # stream-K (64-body units: several fold groups), scalar, orderings, cluster multicast / DSMEM, small family
     with nb.Simulation(n, variant=vid) as sim:
         sim.upload(x0).step(2)
         x, v, a = sim.download()
@@ -21,6 +21,10 @@ for vid in ids:                            # stream-K, scalar, prefetch modes, o
         if vid == ids[0]:
             frame = sim.render()
             assert frame.shape == (600, 800, 4)
+    if vid in (113, 105):                  # the single-level twins (nbody_params.summation)
+        with nb.Simulation(n, variant=vid, summation=nb.NBODY_SUM_SINGLE) as sim:
+            sim.upload(x0).step(2)
+            assert np.isfinite(sim.download()[2]).all(), vid
 dx = torch.from_numpy(x0).cuda()
 dv3, da3 = torch.zeros(n, 3, device="cuda"), torch.zeros(n, 3, device="cuda")
 nb.simulateHeadless_embParallel_float3(dx, da3, dv3, None, n)        # 12-byte-strided epilogue
@@ -40,6 +44,9 @@ for s in sims:
 torch.cuda.synchronize()
 for s in sims:
     s.close()
+with nb.Simulation(n, devices=[0, 0, 0], exchange=nb.NBODY_EXCHANGE_P2P_EVENTS, variant=113) as grp:   # ONE context over "three devices"
+    grp.upload(x0).step(3)
+    assert np.isfinite(grp.download()[2]).all() and np.isfinite(grp.energy()[1])
 with nb.Simulation(700) as sim:                                       # graph-replayed loop
     sim.upload(nb.ic_uniform(700, seed=2)).step(40)
 print("sanitize target done")
