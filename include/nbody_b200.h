@@ -273,6 +273,11 @@ int nbody_autotune_report(char* buf, size_t buflen);
 int nbody_choose_variant(int n_targets, int n_sources, int sm_count, int* measured);
 /* Variant / grid actually used by ctx (after AUTO resolution). */
 int nbody_ctx_info(nbody_ctx* ctx, int* variant, int* grid_ctas, int* ctas_per_sm, int* sm_count);
+/* *spread = 1 when the step kernel of ctx finishes a target tile whose sources were cut between CTAs in ALL of those
+ * CTAs (each sums and integrates its share of the tile's targets; cooperative launch), 0 when the last CTA to arrive
+ * does it alone.  Chosen for mid-size N (12 288 .. 65 536 bodies, many cuts per tile); the sums and their order are
+ * the same either way, so the results are bit-identical.  NBODY_NO_SPREAD_FIXUP=1 in the environment turns it off. */
+int nbody_ctx_fixup(nbody_ctx* ctx, int* spread);
 /* Multi-device context: number of devices (1 for a plain context), NBODY_EXCHANGE_* in use, and whether
  * the cross-device barrier lives in the step kernel (1) or is expressed with events between streams (0). */
 int nbody_group_info(nbody_ctx* ctx, int* n_devices, int* exchange, int* in_kernel_barrier);

@@ -106,6 +106,7 @@ SIGNATURES = {
     "nbody_choose_variant": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]),
     "nbody_autotune_report": (C.c_int, [C.c_char_p, C.c_size_t]),
     "nbody_ctx_info": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "nbody_ctx_fixup": (C.c_int, [_vp, C.POINTER(C.c_int)]),
     "nbody_ic_uniform": (C.c_int, [_vp, C.c_int, C.c_ulonglong, C.c_float, C.c_float, C.c_float]),
     "nbody_ic_plummer": (C.c_int, [_vp, _vp, C.c_int, C.c_ulonglong]),
 }
@@ -300,8 +301,10 @@ class Simulation:
     def info(self) -> dict:
         v, g, o, s = C.c_int(), C.c_int(), C.c_int(), C.c_int()
         _check(lib.nbody_ctx_info(self._h, C.byref(v), C.byref(g), C.byref(o), C.byref(s)))
+        f = C.c_int()
+        _check(lib.nbody_ctx_fixup(self._h, C.byref(f)))
         return {"variant": v.value, "variant_name": variants()[v.value].split(":")[0],
-                "grid_ctas": g.value, "ctas_per_sm": o.value, "sm_count": s.value}
+                "grid_ctas": g.value, "ctas_per_sm": o.value, "sm_count": s.value, "spread_fixup": bool(f.value)}
 
     def upload(self, x4: np.ndarray, v4: np.ndarray | None = None) -> "Simulation":
         assert x4.shape == (self.n, 4)

@@ -64,20 +64,30 @@ struct Variant {
     int cs, cmode;   // cluster size (1 = none); 1 = TMA multicast of source units, 2 = j-split + DSMEM reduction
     void (*kernel)(const ForceArgs);
     void (*kernel_single)(const ForceArgs);   // the same kernel with single-level summation (null: small-N family)
+    void (*kernel_spread)(const ForceArgs) = nullptr;          // mid-size N: split tiles finished by all their CTAs
+    void (*kernel_spread_single)(const ForceArgs) = nullptr;   // (force_kernel's SPREAD; cooperative launch)
     int small = 0;   // 1: small_kernel (T = targets per CTA, sources split over the CTA's threads, shuffle reduction)
     size_t smem(bool single = false) const { return small ? 0 : (size_t)kStages * UJ * 16 + 16 * kStages + 16 + (cmode == 2 ? (size_t)TI() * 16 : 0) + fold_bytes(T, NT, packed != 0, !single); }
-    void (*entry(bool single) const)(const ForceArgs) { return single && kernel_single ? kernel_single : kernel; }
+    void (*entry(bool single, bool spread = false) const)(const ForceArgs)
+    {
+        if (spread && kernel_spread) return single && kernel_spread_single ? kernel_spread_single : kernel_spread;
+        return single && kernel_single ? kernel_single : kernel;
+    }
     int TI() const { return small ? T : T * NT; }
     int TS() const { return cmode == 1 ? TI() * cs : TI(); }          // targets per worker tile
 };
 
 #define VARIANT(id, T, NT, UJ, UN, PK, MB) \
     { id, "T" #T "_NT" #NT "_UJ" #UJ "_U" #UN "_" #PK "_B" #MB, T, NT, UJ, UN, PK, MB, 1, 0, force_kernel<T, NT, UJ, UN, PK, MB>, force_kernel<T, NT, UJ, UN, PK, MB, 1, 0, 0> }
+// mid-size N: the same kernel also with the spread fix-up of split tiles
+#define MVARIANT(id, T, NT, UJ, UN, PK, MB) \
+    { id, "T" #T "_NT" #NT "_UJ" #UJ "_U" #UN "_" #PK "_B" #MB, T, NT, UJ, UN, PK, MB, 1, 0, force_kernel<T, NT, UJ, UN, PK, MB>, force_kernel<T, NT, UJ, UN, PK, MB, 1, 0, 0>, \
+      force_kernel<T, NT, UJ, UN, PK, MB, 1, 0, kFoldEvery, 1>, force_kernel<T, NT, UJ, UN, PK, MB, 1, 0, 0, 1> }
 #define CVARIANT(id, T, NT, UJ, UN, PK, MB, CS, CM) \
     { id, "T" #T "_NT" #NT "_UJ" #UJ "_U" #UN "_" #PK "_B" #MB "_C" #CS "m" #CM, T, NT, UJ, UN, PK, MB, CS, CM, force_kernel<T, NT, UJ, UN, PK, MB, CS, CM>, force_kernel<T, NT, UJ, UN, PK, MB, CS, CM, 0> }
 
 #define SVARIANT(id, TT, NT, UN) \
-    { id, "S_TT" #TT "_NT" #NT "_U" #UN, TT, NT, 64, UN, 1, 1, 1, 0, small_kernel<TT, NT, UN>, nullptr, 1 }
+    { id, "S_TT" #TT "_NT" #NT "_U" #UN, TT, NT, 64, UN, 1, 1, 1, 0, small_kernel<TT, NT, UN>, nullptr, nullptr, nullptr, 1 }
 // packed: 0 = scalar FFMA path (kept as the with/without evidence of the f32x2 choice), 1 = FADD2/FMUL2/FFMA2,
 // 5 / 6 / 7 / 8 = the same packed arithmetic in another source order (bit-identical results; ptxas' register
 // allocation differs by a few per cent, see tuned_large_variant).
@@ -89,7 +99,7 @@ const Variant kVariants[] = {
     VARIANT(9, 4, 256, 256, 4, 0, 2),        // scalar FFMA exemplar
     VARIANT(12, 1, 128, 64, 8, 1, 8),        // fewer than 2 048 targets of many sources
     // large N, 256-body units (12 k .. 64 k sources): one arithmetic, three source orders
-    VARIANT(90, 6, 256, 256, 2, 18, 1),
+    MVARIANT(90, 6, 256, 256, 2, 18, 1),
     VARIANT(97, 6, 256, 256, 2, 7, 1),
     VARIANT(98, 6, 256, 256, 2, 8, 1),
     // large N, 512-body units (>= 64 k sources): one arithmetic, three source orders
@@ -97,11 +107,11 @@ const Variant kVariants[] = {
     VARIANT(102, 6, 256, 512, 2, 7, 1),
     VARIANT(105, 6, 256, 512, 2, 18, 1),
     // mid-size N (cost model in mid_variant): T8 tiles and 64- / 128-body units
-    VARIANT(93, 8, 256, 256, 2, 6, 1),
-    VARIANT(110, 8, 256, 128, 2, 6, 1),
-    VARIANT(111, 8, 256, 64, 2, 6, 1),
-    VARIANT(112, 6, 256, 128, 2, 18, 1),
-    VARIANT(113, 6, 256, 64, 2, 18, 1),
+    MVARIANT(93, 8, 256, 256, 2, 6, 1),
+    MVARIANT(110, 8, 256, 128, 2, 6, 1),
+    MVARIANT(111, 8, 256, 64, 2, 6, 1),
+    MVARIANT(112, 6, 256, 128, 2, 18, 1),
+    MVARIANT(113, 6, 256, 64, 2, 18, 1),
     // thread-block-cluster exemplars (opt-in; measured neutral / slower, profiles/r1_ncu_cluster_evidence.md):
     // m1 = TMA multicast of source units, m2 = j-split with DSMEM reduction
     CVARIANT(60, 6, 256, 256, 2, 1, 1, 2, 1),
@@ -240,7 +250,17 @@ struct Plan {
     int grid = 0, occ = 0, maxseg = 0, num_itiles = 0, num_counters = 0;
     size_t partial_bytes = 0;
     bool single = false;   // single-level summation kernel (nbody_params.summation)
+    bool spread = false;   // split tiles finished by all their CTAs (force_kernel's SPREAD): cooperative launch
 };
+
+constexpr long long kSpreadBelowSources = 65536 + 1024;
+bool g_spread_fixup = getenv("NBODY_NO_SPREAD_FIXUP") == nullptr;   // debugging switch: the last-arriver fix-up everywhere
+bool cooperative_launch_ok()
+{
+    int dev = 0, ok = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return false;
+    return cudaDeviceGetAttribute(&ok, cudaDevAttrCooperativeLaunch, dev) == cudaSuccess && ok != 0;
+}
 
 int make_plan(const Variant* v, int sm_count, int grid_override, int n_targets, int J, Plan* out, bool single = false)
 {
@@ -277,6 +297,17 @@ int make_plan(const Variant* v, int sm_count, int grid_override, int n_targets, 
     if ((unsigned long long)workers > U) workers = (long long)U;
     if (workers < 1) workers = 1;
     pl.grid = (int)workers * v->cs;
+    // Mid-size N: few tiles, each cut into many segments, and the last CTA to arrive would sum them all alone.
+    // Spread that over the tile's CTAs when the launch can be cooperative (the CTAs wait for each other).  Measured
+    // (tools/experiment_spread.sh): 120.1 -> 113.3 us at N = 16 384, 74.7 -> 71.9 us at 12 288, nothing from 24 576
+    // up, where a tile has 12 segments or fewer; at large N the fix-up is < 0.1 % of the step and the launch stays plain.
+    if (v->kernel_spread && g_spread_fixup && (long long)J * v->UJ < kSpreadBelowSources && workers >= 4LL * pl.num_itiles &&
+        cooperative_launch_ok()) {
+        int occ = 0;
+        CU(cudaFuncSetAttribute(v->entry(pl.single, true), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v->smem(pl.single)));
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, v->entry(pl.single, true), v->NT, v->smem(pl.single)));
+        pl.spread = workers <= (long long)sm_count * occ;
+    }
     const unsigned long long q = U / (unsigned long long)workers;   // smallest range, >= 1 when U > 0
     pl.maxseg = q > 0 ? (int)((unsigned long long)(J - 1) / q) + 2 : 2;
     pl.num_counters = pl.num_itiles * v->cs;
@@ -288,7 +319,15 @@ int make_plan(const Variant* v, int sm_count, int grid_override, int n_targets, 
 int launch_force(const Variant* v, const Plan& pl, const ForceArgs& args_in, cudaStream_t st)
 {
     const ForceArgs& args = args_in;
-    if (v->cs > 1) {
+    if (pl.spread) {
+        cudaLaunchConfig_t cfg = {};
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeCooperative;
+        at[0].val.cooperative = 1;
+        cfg.gridDim = dim3(pl.grid); cfg.blockDim = dim3(v->NT); cfg.dynamicSmemBytes = v->smem(pl.single); cfg.stream = st;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        CU(cudaLaunchKernelEx(&cfg, v->entry(pl.single, true), args));
+    } else if (v->cs > 1) {
         cudaLaunchConfig_t cfg = {};
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeClusterDimension;
@@ -676,6 +715,14 @@ int nbody_ctx_info(nbody_ctx* c, int* variant, int* grid_ctas, int* ctas_per_sm,
     if (grid_ctas) *grid_ctas = c->plan_full.grid;
     if (ctas_per_sm) *ctas_per_sm = c->plan_full.occ;
     if (sm_count) *sm_count = c->sm_count;
+    return NBODY_OK;
+}
+
+int nbody_ctx_fixup(nbody_ctx* c, int* spread)
+{
+    if (!c || !spread) return fail(NBODY_E_INVALID, "null argument");
+    if (!c->kids.empty()) c = c->kids[0];
+    *spread = c->plan_full.spread ? 1 : 0;
     return NBODY_OK;
 }
 

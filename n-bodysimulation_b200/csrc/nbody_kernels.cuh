@@ -176,7 +176,11 @@ __device__ __forceinline__ int unit_owner(u64 u, u64 U, u64 W) { return (int)(((
 //           the segment; the partial sums are combined through distributed shared memory
 //           (ld.shared::cluster, fixed rank order), CTA r finishing slice r of the tile.
 // FOLDK: source units per first-level sum (0 = single-level summation, nbody_params.summation = NBODY_SUM_SINGLE)
-template <int T, int NT, int UJ, int UNROLL, int MODE, int MINB, int CS = 1, int CMODE = 0, int FOLDK = kFoldEvery>
+// SPREAD 1: the fix-up of a split tile is spread over the CTAs that worked on it (each sums and integrates 1 / nseg of
+//        the tile's targets once all partial sums are there) instead of falling to the last one to arrive.  The CTAs
+//        wait for each other, so the launch must be cooperative (whole grid resident).  Same sums in the same order.
+//        A separate instantiation (mid-size N only): the large-N kernels keep their code and register allocation.
+template <int T, int NT, int UJ, int UNROLL, int MODE, int MINB, int CS = 1, int CMODE = 0, int FOLDK = kFoldEvery, int SPREAD = 0>
 __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
 {
     constexpr bool PACKED = MODE != 0;
@@ -200,6 +204,7 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
     static_assert((FOLDK & (FOLDK - 1)) == 0, "fold group must be a power of two (or 0 = off)");
     static_assert((UJ / 2) % UNROLL == 0, "unroll must divide the pairs per unit");
     static_assert(CS == 1 || CMODE == 1 || CMODE == 2, "cluster variants need a mode");
+    static_assert(!SPREAD || CS == 1, "the spread fix-up is for the non-cluster kernels");
     static_assert(!MCAST || (kStageBytes / CS) % 16 == 0, "multicast slices must be 16-byte multiples");
     static_assert(!JSPLIT || (TI / CS) % 32 == 0, "j-split slices must be whole warps");
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -294,6 +299,11 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
 
     const u64 eps2p = pack2(a.eps2, a.eps2);
     int k = 0;   // units consumed so far
+    // SPREAD: the split segments of this CTA (a contiguous unit range has at most two: the tail of its first tile
+    // and the head of its last), to be finished after the loop: {tile or -1, segments of the tile << 16 | this CTA's
+    // index} twice, in the 16 bytes of s_flag (unused in this mode) so that nothing more stays live across the loop
+    volatile int* s_pend = s_flag;
+    if (SPREAD && tid == 0) { s_pend[0] = -1; s_pend[2] = -1; }
     u64 u = u_begin;
     while (u < u_end) {
         const int it = (int)(u / (u64)J);
@@ -480,6 +490,15 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
                 for (int t = 0; t < T; ++t) slot[tid + t * NT] = make_float4(fx[t], fy[t], fz[t], 0.f);
                 __threadfence();
                 __syncthreads();
+                if (SPREAD) {   // counted now, finished by all of the tile's CTAs after the loop
+                    if (tid == 0) {
+                        atomicAdd(&a.counters[vt], 1u);
+                        const int at = s_pend[0] < 0 ? 0 : 2;
+                        s_pend[at] = vt; s_pend[at + 1] = (nseg << 16) | ((int)w - w_first);
+                    }
+                    u += (u64)jn;
+                    continue;
+                }
                 if (tid == 0) {
                     const unsigned old = atomicAdd(&a.counters[vt], 1u);
                     *s_flag = (old == (unsigned)(nseg - 1));
@@ -571,6 +590,45 @@ __global__ void __launch_bounds__(NT, MINB) force_kernel(const ForceArgs a)
             }
         }
         u += (u64)jn;
+    }
+    if (SPREAD) {
+        // ---- spread fix-up: CTA number ix of the nseg that worked on a split tile finishes slice ix of its targets
+        // (whole warps), summing the nseg partial sums in segment order exactly as the last-arriver path does.  With
+        // a tile cut 18 ways (N = 16 384) the last arriver alone reads 18 x TI x 16 B = 590 KB through one SM while
+        // 140 SMs idle (13 us of a 126 us kernel, profiles/r2_ncu_full_16k_raw.csv: SM active min / avg / max 177k /
+        // 205k / 231k cycles); spread, every SM reads 32 KB.
+        __syncthreads();
+        for (int q = 0; q < 2; ++q) {
+            const int vt = s_pend[2 * q];
+            if (vt < 0) break;
+            const int nseg = s_pend[2 * q + 1] >> 16, ix = s_pend[2 * q + 1] & 0xffff;
+            if (tid == 0) {
+                const unsigned long long t0 = globaltimer_ns();
+                while (ld_acquire_gpu_u32(a.counters + vt) < (unsigned)nseg) {
+                    if (globaltimer_ns() - t0 > 4000000000ull) __trap();   // cannot happen on a cooperative launch
+                }
+            }
+            __syncthreads();
+            __threadfence();
+            const int chunk = (((TI + nseg - 1) / nseg) + 31) & ~31;
+            const int i_end = (ix + 1) * chunk < TI ? (ix + 1) * chunk : TI;
+            const float4* tile_part = a.partial + (size_t)vt * a.maxseg * TI;
+            for (int i = ix * chunk + tid; i < i_end; i += NT) {
+                float rx = 0.f, ry = 0.f, rz = 0.f;
+#pragma unroll 4
+                for (int sg = 0; sg < nseg; ++sg) {
+                    const float4 p = __ldcg(tile_part + (size_t)sg * TI + i);
+                    rx = __fadd_rn(rx, p.x); ry = __fadd_rn(ry, p.y); rz = __fadd_rn(rz, p.z);
+                }
+                const int gi = vt * TI + i;
+                integrate_one(a, gi, gi < a.n_targets, rx, ry, rz, lane);
+            }
+            __syncthreads();
+            if (tid == 0) {   // the last CTA to finish its slice leaves the counter at zero for the next launch
+                const unsigned old = atomicAdd(&a.counters[vt], 1u);
+                if (old == 2u * (unsigned)nseg - 1u) a.counters[vt] = 0u;
+            }
+        }
     }
     if (a.clk && blockIdx.x == 0 && tid == 0) { a.clk[2] = clock64(); a.clk[3] = globaltimer_ns(); }
     if (a.bar_flags) {

@@ -56,6 +56,12 @@ __device__ __forceinline__ unsigned long long globaltimer_ns()
 }
 
 // ---- system-scope flags (cross-GPU barrier of the fused exchange) ---------------------------
+__device__ __forceinline__ unsigned ld_acquire_gpu_u32(const unsigned* p)
+{
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long* p)
 {
     unsigned long long v;
