@@ -299,9 +299,11 @@ int make_plan(const Variant* v, int sm_count, int grid_override, int n_targets, 
     pl.grid = (int)workers * v->cs;
     // Mid-size N: few tiles, each cut into many segments, and the last CTA to arrive would sum them all alone.
     // Spread that over the tile's CTAs when the launch can be cooperative (the CTAs wait for each other).  Measured
-    // (tools/experiment_spread.sh): 120.1 -> 113.3 us at N = 16 384, 74.7 -> 71.9 us at 12 288, nothing from 24 576
-    // up, where a tile has 12 segments or fewer; at large N the fix-up is < 0.1 % of the step and the launch stays plain.
-    if (v->kernel_spread && g_spread_fixup && (long long)J * v->UJ < kSpreadBelowSources && workers >= 4LL * pl.num_itiles &&
+    // (tools/experiment_spread.sh, profiles/r2_spread_fixup.txt), spread | last arriver: 73.1 | 76.1 us at N = 12 288,
+    // 114.0 | 116.9 us at 16 384, 174.8 | 176.1 us at 20 480; with 12 or fewer cuts per tile (24 576 bodies and up) the
+    // fix-up is too small to matter and the other instantiation's register allocation costs more than it saves
+    // (252 | 242 us at 24 576), so the rule asks for 14 cuts per tile.
+    if (v->kernel_spread && g_spread_fixup && (long long)J * v->UJ < kSpreadBelowSources && workers >= 14LL * pl.num_itiles &&
         cooperative_launch_ok()) {
         int occ = 0;
         CU(cudaFuncSetAttribute(v->entry(pl.single, true), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v->smem(pl.single)));
