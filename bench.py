@@ -59,6 +59,9 @@ def parse():
     ap.add_argument("--cpu-series", action="store_true",
                     help="with --impl reference: also print baseline B1 of BASELINE.md (reference CPU path at N=1024x10, 16384x3, "
                          "131072x1, -O2 and -O3 builds) as extra JSON lines BEFORE the contract line")
+    ap.add_argument("--ref-kernel-noguard", type=int, default=0, metavar="N",
+                    help="--impl reference: also time ONE step of the reference kernel.cu at N bodies with its launcher's "
+                         "total-shared-memory guard dropped (oracle/_ref/libref_kernel_sm100_noguard.so; N = 8388608 takes ~100 s); needs a GPU")
     ap.add_argument("--ref-kernel-series", action="store_true",
                     help="with --impl reference: also print baseline B2 of BASELINE.md (the reference's kernel.cu rebuilt for sm_100, "
                          "oracle/_ref/libref_kernel_sm100*.so, as shipped and re-tuned to 256 threads) as extra JSON lines; needs a GPU")
@@ -248,13 +251,27 @@ def ref_kernel_series():
                 print(json.dumps({"baseline": label, "n": n, "ms_per_step": round(r[0], 3), "g_inter_per_s": round(r[1], 2)}), flush=True)
     print(json.dumps({"baseline": "B2 reference kernel.cu rebuilt for sm_100", "n": 8388608,
                       "error": "the reference's launcher throws \"Shared memory request too large.\" (kernel.cu:639-641): 16*N B > 228 KiB x 148 SMs; "
-                               "not called here (a C++ exception through ctypes aborts the process); a guard-bypassed run would take ~100 s per step"}), flush=True)
+                               "not called here (a C++ exception through ctypes aborts the process); guard bypassed: --ref-kernel-noguard 8388608 (96.5 s per step = 729 G/s, profiles/r2_reference_kernel_noguard_8m.json)"}), flush=True)
+
+
+def ref_kernel_noguard(n):
+    """BASELINE.md section 3, B2 at N = 8 388 608: the reference launcher refuses this size ("Shared memory request too
+    large.", kernel.cu:639-641); the same kernel.cu with that half of the guard dropped, one step, labelled as such"""
+    ref_kernel_rate("libref_kernel_sm100_noguard.so", 16384, 1, 0)     # context + module load outside the timed step
+    r = ref_kernel_rate("libref_kernel_sm100_noguard.so", n, 1, 0)
+    if r:
+        print(json.dumps({"baseline": "B2 reference kernel.cu rebuilt for sm_100, launcher guard BYPASSED (kernel.cu:639-641, second half of the condition dropped in a /tmp copy; not the reference as shipped)",
+                          "n": n, "steps": 1, "ms_per_step": round(r[0], 1), "g_inter_per_s": round(r[1], 2)}), flush=True)
+    else:
+        print(json.dumps({"baseline": "B2 guard bypassed", "error": "oracle/_ref/libref_kernel_sm100_noguard.so not built"}), flush=True)
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    if args.ref_kernel_noguard:
+        ref_kernel_noguard(args.ref_kernel_noguard)
     if args.cpu_series:
         cpu_series()
     if args.ref_kernel_series:
