@@ -70,6 +70,9 @@ if rank == 0:
     for k, (p_, q_) in {"a": (A, ar), "v": (V, vr), "x": (X, xr)}.items():
         e_ = np.linalg.norm((p_ - q_)[:, :3].astype(np.float64), axis=1) / np.maximum(np.linalg.norm(q_[:, :3].astype(np.float64), axis=1), 1e-300)
         res[f"p99.9_{k}"], res[f"median_{k}"] = float(np.quantile(e_, 0.999)), float(np.median(e_))
+    # the flat bounds of SURVEY.md section 8c (no allowance for the spread between summation orders): met since the
+    # two-level summation of round 2 for one step; over several steps close pairs amplify rounding differences
+    res["strict_ok"] = bool(sim_timeouts == 0 and len(X) == n and res["err_x"] <= 1e-6 and res["err_v"] <= 1e-5 and res["err_a"] <= 1e-5)
     res["ok"] = bool(sim_timeouts == 0 and len(X) == n and res["err_x"] <= tol_x and res["err_v"] <= tol_v and res["err_a"] <= tol_a)
     print(json.dumps(res), flush=True)
     rc = 0 if res["ok"] else 1
