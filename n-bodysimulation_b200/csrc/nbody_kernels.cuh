@@ -13,7 +13,9 @@
 //     contiguous ranges, one per persistent CTA ("stream-K" style), so that all
 //     148 SMs finish together at any N.  A target tile whose source range is
 //     split between CTAs is completed by the LAST CTA to arrive, which adds the
-//     partial sums in fixed segment order (deterministic) and integrates;
+//     partial sums in fixed segment order (deterministic) and integrates -- or, at
+//     mid-size N where a tile has many cuts, by ALL of its CTAs, 1 / nseg of the
+//     targets each (SPREAD, cooperative launch; same sums, same order);
 //   * snapshot-pure: sources are read from the packed buffer of the step's
 //     start, new positions go to the other packed buffer.
 #pragma once
