@@ -186,14 +186,24 @@ int mid_variant(int n_targets, int n_sources, int sms);
 // The static part of the choice (best of the r1 sweeps, profiles/r1_variant_sweep_*.jsonl; the cluster variants
 // 60-70 measured neutral (C2 multicast) or slower (C4/C8, DSMEM j-split) and are opt-in only).
 // *measured = true: one of the equivalent large-N kernels, to be picked by tuned_large_variant().
+int env_int(const char* name, int dflt)
+{
+    const char* e = getenv(name);
+    return e && *e ? atoi(e) : dflt;
+}
+// Bodies below which the small-N family runs.  Measured with the spread fix-up (tools/experiment_small_below.sh,
+// profiles/r2_small_below.txt): from 10 240 bodies up the stream-K kernels win every size tried (3 - 15 %); between
+// 5 632 and 9 728 the two alternate with the rounding of units per CTA / CTAs per wave, so the rule stays simple.
+// NBODY_SMALL_BELOW in the environment moves it (tuning switch).
+const int g_small_below = env_int("NBODY_SMALL_BELOW", 10240);
 int static_variant(int n_targets, int n_sources, int sms, bool* measured)
 {
     *measured = false;
-    if (n_sources < 12288) {             // a step is < 50 us: latency decides -> small-N family
+    if (n_sources < g_small_below) {     // a step is < 50 us: latency decides -> small-N family
         if (n_sources < 3072) return 85; // 2 targets / CTA, sources split over 128 threads, shuffle reduction
         return 82;                       // 4 targets / CTA
     }
-    if (n_targets >= 12288 && n_sources < 65536) return mid_variant(n_targets, n_sources, sms);
+    if (n_targets >= g_small_below && n_sources < 65536) return mid_variant(n_targets, n_sources, sms);
     if (n_targets >= 12288) { *measured = true; return n_sources < 65536 ? 90 : 101; }
     if (n_targets >= 2048) return 3;     // T2 x 256 threads, 3 CTAs/SM
     return 12;                           // T1 x 128 threads, 64-body units
