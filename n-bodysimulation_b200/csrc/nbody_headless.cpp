@@ -13,6 +13,8 @@
 //                  [--flavour simulate|emb|emb-float3]   which launcher of kernel.cuh:2-7 (headless forms)
 //                  [--ppm FILE]                          final frame (the reference's GL draw as CUDA)
 //                  [--save FILE] [--load FILE]           snapshot / resume (with --resident)
+//                  [--energy]                            with --resident: a second JSON line with KE, PE before / after and
+//                                                        the relative drift of E_eff = KE + PE / 2 (BASELINE's drift bound)
 //                  [--gpus G]                            G GPUs of this box from ONE process: with --resident ONE multi-device
 //                                                        context (each device owns N/G targets; --exchange p2p|nccl), else
 //                                                        simulate_set_devices(G): the reference's loop over simulate() with
@@ -76,7 +78,7 @@ int main(int argc, char** argv)
     unsigned long long seed = 12345;
     float eps2 = EPS2, dt = DT;
     std::string ic = "reference", flavour = "simulate", exchange = "p2p", ppm, save, load;
-    bool resident = false, host_f3 = false, json = false;
+    bool resident = false, host_f3 = false, json = false, energy = false;
     int gpus = 1;
     for (int i = 1; i < argc; ++i) {
         auto need = [&](const char* f) { if (i + 1 >= argc) { fprintf(stderr, "%s needs a value\n", f); exit(2); } return argv[++i]; };
@@ -89,6 +91,7 @@ int main(int argc, char** argv)
         else if (!strcmp(argv[i], "--resident")) resident = true;
         else if (!strcmp(argv[i], "--host-f3")) host_f3 = true;
         else if (!strcmp(argv[i], "--json")) json = true;
+        else if (!strcmp(argv[i], "--energy")) energy = true;
         else if (!strcmp(argv[i], "--gpus")) gpus = atoi(need("--gpus"));
         else if (!strcmp(argv[i], "--flavour")) flavour = need("--flavour");
         else if (!strcmp(argv[i], "--exchange")) exchange = need("--exchange");
@@ -98,6 +101,7 @@ int main(int argc, char** argv)
         else { fprintf(stderr, "unknown flag %s\n", argv[i]); return 2; }
     }
     if (n <= 0 || steps < 0) { fprintf(stderr, "bad --n / --steps\n"); return 2; }
+    if (energy && !resident) { fprintf(stderr, "--energy needs --resident\n"); return 2; }
     if ((!save.empty() || !load.empty()) && !resident) { fprintf(stderr, "--save / --load need --resident\n"); return 2; }
     if (flavour != "simulate" && flavour != "emb" && flavour != "emb-float3") { fprintf(stderr, "unknown --flavour %s\n", flavour.c_str()); return 2; }
     if (exchange != "p2p" && exchange != "nccl") { fprintf(stderr, "unknown --exchange %s\n", exchange.c_str()); return 2; }
@@ -120,6 +124,7 @@ int main(int argc, char** argv)
 
     int rc = 0;
     float ms = -1.f, ms_first = -1.f, ms_steady = -1.f;
+    double ke0 = 0, pe0 = 0, ke1 = 0, pe1 = 0;   // --energy: KE and pair potential before / after (conserved: KE + PE / 2)
     if (gpus > 1 && resident) {
         // ONE context spanning G devices (nbody_params.n_devices): the library owns the per-device shards, the peer
         // mapping, the exchange (--exchange p2p: fused into the step kernel, in-kernel flag barrier; nccl: ncclAllGather
@@ -134,10 +139,12 @@ int main(int argc, char** argv)
             std::cerr << nbody_last_error() << std::endl;
             return EXIT_FAILURE;
         }
+        if (energy && nbody_energy(ctx, &ke0, &pe0)) { std::cerr << nbody_last_error() << std::endl; return EXIT_FAILURE; }
         printf("Starting the simulation...\n");
         if (nbody_step(ctx, steps)) { std::cerr << nbody_last_error() << std::endl; rc = EXIT_FAILURE; }
         else printf("Simulation complete\n");
         nbody_elapsed_ms(ctx, &ms);
+        if (energy && rc == 0 && nbody_energy(ctx, &ke1, &pe1)) { std::cerr << nbody_last_error() << std::endl; rc = EXIT_FAILURE; }
         int timed_out = 0;
         nbody_shard_barrier_timeouts(ctx, &timed_out);
         if (timed_out) { std::cerr << "cross-GPU barrier timed out " << timed_out << " time(s): state invalid" << std::endl; rc = EXIT_FAILURE; }
@@ -166,10 +173,12 @@ int main(int argc, char** argv)
             std::cerr << nbody_last_error() << std::endl;
             return EXIT_FAILURE;
         }
+        if (energy && nbody_energy(ctx, &ke0, &pe0)) { std::cerr << nbody_last_error() << std::endl; return EXIT_FAILURE; }
         printf("Starting the simulation...\n");
         if (nbody_step(ctx, steps)) { std::cerr << nbody_last_error() << std::endl; rc = EXIT_FAILURE; }
         else printf("Simulation complete\n");
         nbody_elapsed_ms(ctx, &ms);
+        if (energy && rc == 0 && nbody_energy(ctx, &ke1, &pe1)) { std::cerr << nbody_last_error() << std::endl; rc = EXIT_FAILURE; }
         nbody_download(ctx, (float*)bodies, (float*)velocity, (float*)accelerations);
         if (!save.empty() && nbody_snapshot_save(ctx, save.c_str())) { std::cerr << nbody_last_error() << std::endl; rc = EXIT_FAILURE; }
         nbody_destroy(ctx);
@@ -237,6 +246,11 @@ int main(int argc, char** argv)
                n, steps, ic.c_str(), host_f3 ? "host-f3" : resident ? "resident" : flavour.c_str(), ms, ms > 0 ? inter / (ms * 1e-3) / 1e9 : 0.0,
                ms_first, ms_steady, ms_steady > 0 ? (double)n * (double)n / (ms_steady * 1e-3) / 1e9 : 0.0,
                checksum(bodies, n), checksum(velocity, n), nbody_launch_count(), gpus, gpus > 1 && resident ? exchange.c_str() : gpus > 1 ? "set_devices" : "none");
+        if (energy) {
+            const double e0 = ke0 + 0.5 * pe0, e1 = ke1 + 0.5 * pe1;
+            printf("{\"energy\": \"E_eff = KE + PE / 2\", \"ke0\": %.9e, \"pe0\": %.9e, \"ke1\": %.9e, \"pe1\": %.9e, \"e_eff0\": %.9e, \"e_eff1\": %.9e, \"rel_drift\": %.3e}\n",
+                   ke0, pe0, ke1, pe1, e0, e1, e0 != 0 ? (e1 - e0) / (e0 < 0 ? -e0 : e0) : 0.0);
+        }
     }
     nbody_release_cached();
     cudaFreeHost(bodies); cudaFreeHost(velocity); cudaFreeHost(accelerations);

@@ -170,3 +170,14 @@ def test_spread_fixup_of_split_tiles_same_bits_as_the_last_arriver(cuda, nb, n):
         assert r.returncode == 0, r.stderr[-400:]
         b = result(r)
         assert a["checksum_x"] == b["checksum_x"] and a["checksum_v"] == b["checksum_v"]
+
+
+def test_energy_lines_of_a_resident_run(cuda):
+    # BASELINE's drift bound through the driver: Plummer sphere, dt = 0.01, |E_eff drift| <= 1e-3 over 100 steps
+    # (tests/test_parity_gpu.py holds the same bound at config 3 through the C ABI)
+    r = headless("--n", 20000, "--steps", 100, "--ic", "plummer", "--seed", 9, "--dt", 0.01, "--resident", "--energy", "--json")
+    lines = [json.loads(ln) for ln in r.stdout.splitlines() if ln.startswith("{")]
+    assert len(lines) == 2 and "rel_drift" in lines[1]
+    e = lines[1]
+    assert e["ke0"] > 0 and e["pe0"] < 0 and abs(e["rel_drift"]) <= 1e-3, e
+    assert headless("--n", 100, "--energy", ok=False).returncode == 2      # needs --resident
