@@ -266,7 +266,7 @@ int nbody_variant_id(int index);
  * guessing.  Environment NBODY_LARGE_VARIANT=<id> forces the choice. */
 int nbody_autotune_report(char* buf, size_t buflen);
 /* The kernel variant NBODY_VARIANT_AUTO resolves to for a context owning n_targets of n_sources
- * bodies on a device with sm_count SMs, by the static rules alone (small-N family below 10 240
+ * bodies on a device with sm_count SMs, by the static rules alone (small-N family below 8 192
  * sources, tile shape x unit size by unit balance up to 65 536, one of the measured candidates
  * above -- for that last case the id returned is the first candidate and *measured is set to 1:
  * the real choice is timed on the device).  Host-only; needs no GPU. */
@@ -275,7 +275,7 @@ int nbody_choose_variant(int n_targets, int n_sources, int sm_count, int* measur
 int nbody_ctx_info(nbody_ctx* ctx, int* variant, int* grid_ctas, int* ctas_per_sm, int* sm_count);
 /* *spread = 1 when the step kernel of ctx finishes a target tile whose sources were cut between CTAs in ALL of those
  * CTAs (each sums and integrates its share of the tile's targets; cooperative launch), 0 when the last CTA to arrive
- * does it alone.  Chosen for mid-size N (10 240 .. 20 480 bodies: 14 or more cuts per tile); the sums and their order are
+ * does it alone.  Chosen for mid-size N (8 192 .. 20 480 bodies: 14 or more cuts per tile); the sums and their order are
  * the same either way, so the results are bit-identical.  NBODY_NO_SPREAD_FIXUP=1 in the environment turns it off. */
 int nbody_ctx_fixup(nbody_ctx* ctx, int* spread);
 /* Multi-device context: number of devices (1 for a plain context), NBODY_EXCHANGE_* in use, and whether

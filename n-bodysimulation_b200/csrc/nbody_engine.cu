@@ -192,10 +192,11 @@ int env_int(const char* name, int dflt)
     return e && *e ? atoi(e) : dflt;
 }
 // Bodies below which the small-N family runs.  Measured with the spread fix-up (tools/experiment_small_below.sh,
-// profiles/r2_small_below.txt): from 10 240 bodies up the stream-K kernels win every size tried (3 - 15 %); between
-// 5 632 and 9 728 the two alternate with the rounding of units per CTA / CTAs per wave, so the rule stays simple.
+// profiles/r2_small_below.txt, best of three 3 200-step runs per size): from 8 192 bodies up the stream-K kernels tie
+// or win at every size tried (0 .. 15 %); between 5 632 and 7 680 the two alternate with the rounding of units per
+// CTA / CTAs per wave (+8 % at 6 144, -7 % at 7 680), so the rule stays simple.
 // NBODY_SMALL_BELOW in the environment moves it (tuning switch).
-const int g_small_below = env_int("NBODY_SMALL_BELOW", 10240);
+const int g_small_below = env_int("NBODY_SMALL_BELOW", 8192);
 int static_variant(int n_targets, int n_sources, int sms, bool* measured)
 {
     *measured = false;

@@ -211,7 +211,7 @@ def test_multi_device_context_matches_one_gpu(cuda, nb, oracle, tmp_path, n, exc
     ex = {"p2p": nb.NBODY_EXCHANGE_P2P, "nccl": nb.NBODY_EXCHANGE_NCCL, "p2p-events": nb.NBODY_EXCHANGE_P2P_EVENTS}[exchange]
     gi = check_group(nb, oracle, n, list(range(G)), ex, tmp_path=tmp_path)
     assert gi["exchange"] == exchange
-    assert gi["in_kernel_barrier"] == (exchange == "p2p" and n >= 10240)      # the small-N family is ordered by events
+    assert gi["in_kernel_barrier"] == (exchange == "p2p" and n >= 8192)      # the small-N family is ordered by events
 
 
 def test_simulate_spread_over_devices(cuda, nb, oracle):
