@@ -339,7 +339,15 @@ int launch_force(const Variant* v, const Plan& pl, const ForceArgs& args_in, cud
         at[0].val.cooperative = 1;
         cfg.gridDim = dim3(pl.grid); cfg.blockDim = dim3(v->NT); cfg.dynamicSmemBytes = v->smem(pl.single); cfg.stream = st;
         cfg.attrs = at; cfg.numAttrs = 1;
-        CU(cudaLaunchKernelEx(&cfg, v->entry(pl.single, true), args));
+        const cudaError_t e = cudaLaunchKernelEx(&cfg, v->entry(pl.single, true), args);
+        if (e == cudaErrorCooperativeLaunchTooLarge) {
+            // fewer SMs than the plan saw (MPS with an SM limit, a green context): the last-arriver kernel needs no
+            // co-residency and gives the same bits
+            (void)cudaGetLastError();
+            v->entry(pl.single)<<<pl.grid, v->NT, v->smem(pl.single), st>>>(args);
+        } else {
+            CU(e);
+        }
     } else if (v->cs > 1) {
         cudaLaunchConfig_t cfg = {};
         cudaLaunchAttribute at[1];
