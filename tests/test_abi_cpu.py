@@ -63,6 +63,8 @@ def test_argument_validation(nb):
     assert nb.lib.nbody_step_inplace_f4(None, None, None, 16, 0.002, 0.1) == -1
     assert nb.lib.nbody_step_inplace_f4(1, 1, 1, 0, 0.002, 0.1) == -1
     assert nb.lib.nbody_step_host_f3(None, None, None, 4, 0.002, 0.01) == -1
+    f = C.c_int(7)
+    assert nb.lib.nbody_ctx_fixup(None, C.byref(f)) == -1 and f.value == 7 and b"null" in nb.lib.nbody_last_error()
 
 
 def test_multi_device_parameters_are_validated_on_the_host(nb):
