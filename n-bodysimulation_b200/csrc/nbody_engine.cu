@@ -230,10 +230,12 @@ int mid_variant(int n_targets, int n_sources, int sms)
         sms = 148;
         if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     }
-    const long long src_pad = (long long)(n_sources + kSlotAlign - 1) / kSlotAlign * kSlotAlign;
+    // an unsharded context visits the units up to its last body; a shard sees the other shards' slots, padded to kSlotAlign
+    const bool whole = n_targets == n_sources;
     double best_cost = 1e300;
     int best = 90;
     for (const Cand& c : cands) {
+        const long long src_pad = whole ? (long long)(n_sources + c.UJ - 1) / c.UJ * c.UJ : (long long)(n_sources + kSlotAlign - 1) / kSlotAlign * kSlotAlign;
         const long long tiles = (n_targets + c.T * 256 - 1) / (c.T * 256), J = src_pad / c.UJ, U = tiles * J;
         const long long maxu = (U + sms - 1) / sms;
         // cycles per unit: UJ/4 loop iterations of (T x 24 packed ops x 2 + ~35) cycles, plus ~150 of barrier / producer work
@@ -530,11 +532,25 @@ int set_device(nbody_ctx* c)
     return NBODY_OK;
 }
 
+// Source units a step visits: the packed buffer is padded to kSlotAlign bodies per shard (zero-mass bodies), but
+// the units behind the last real body hold nothing and are not visited (N = 7 680: 120 units of 64, not 128).
+int units_in_use(const nbody_ctx* c)
+{
+    const int UJ = c->var->UJ, last = c->n - (c->p.world - 1) * c->per;   // bodies of the last shard
+    return ((c->p.world - 1) * c->slot_bodies + round_up(last, UJ)) / UJ;
+}
+
+// ... and of this shard's own slot (the last shard's slot ends early)
+int units_own_in_use(const nbody_ctx* c)
+{
+    const int own = c->slot_bodies / c->var->UJ, left = units_in_use(c) - c->p.rank * own;
+    return left < own ? left : own;
+}
+
 // launch plans of c->var for this context's geometry + the split-tile scratch they need
 int plan_scratch(nbody_ctx* c)
 {
-    const int UJ = c->var->UJ;
-    const int units_total = c->n_src_pad / UJ, units_own = c->slot_bodies / UJ;
+    const int units_total = units_in_use(c), units_own = units_own_in_use(c);
     const bool single = c->p.summation == NBODY_SUM_SINGLE;
     int rc = make_plan(c->var, c->sm_count, c->p.grid_ctas, c->n_targets, units_total, &c->plan_full, single);
     if (rc) return rc;

@@ -19,7 +19,7 @@ inline bool is_group(const nbody_ctx* c) { return !c->kids.empty(); }
 int enqueue_full_step(nbody_ctx* c, cudaStream_t st)
 {
     ForceArgs a = base_args(c);
-    a.ra_begin = 0; a.ra_count = c->n_src_pad / c->var->UJ;
+    a.ra_begin = 0; a.ra_count = units_in_use(c);
     a.rb_begin = 0; a.rb_count = 0;
     a.next_src = c->packed[c->cur ^ 1];
     a.next_off = c->p.rank * c->slot_bodies;
@@ -257,7 +257,7 @@ int nbody_shard_local_async(nbody_ctx* c, void* stream)
     if (c->p.world == 1) return enqueue_full_step(c, st);   // nothing remote: one fused launch
     const int UJ = c->var->UJ, own = c->slot_bodies / UJ;
     ForceArgs a = base_args(c);
-    a.ra_begin = c->p.rank * own; a.ra_count = own;
+    a.ra_begin = c->p.rank * own; a.ra_count = units_own_in_use(c);
     a.accum_out = c->accum;
     a.maxseg = c->plan_local.maxseg;
     return launch_force(c->var, c->plan_local, a, st);
@@ -272,10 +272,10 @@ int nbody_shard_remote_async(nbody_ctx* c, void* stream)
     if (rc) return rc;
     if (c->p.world == 1) return NBODY_OK;
     cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
-    const int UJ = c->var->UJ, own = c->slot_bodies / UJ, total = c->n_src_pad / UJ;
+    const int UJ = c->var->UJ, own = c->slot_bodies / UJ, total = units_in_use(c);
     ForceArgs a = base_args(c);
     a.ra_begin = 0; a.ra_count = c->p.rank * own;
-    a.rb_begin = (c->p.rank + 1) * own; a.rb_count = total - a.rb_begin;
+    a.rb_begin = (c->p.rank + 1) * own; a.rb_count = total > a.rb_begin ? total - a.rb_begin : 0;   // the last shard has nothing behind it
     a.accum_in = c->accum;
     a.next_src = c->packed[c->cur ^ 1];
     a.next_off = c->p.rank * c->slot_bodies;
@@ -369,7 +369,7 @@ int nbody_shard_step_fused_async(nbody_ctx* c, void* stream)
     if (c->p.world == 1) return enqueue_full_step(c, st);
     if (c->peers_attached != c->p.world - 1) return fail(NBODY_E_STATE, "%d of %d peers attached", c->peers_attached, c->p.world - 1);
     ForceArgs a = base_args(c);
-    a.ra_begin = 0; a.ra_count = c->n_src_pad / c->var->UJ;
+    a.ra_begin = 0; a.ra_count = units_in_use(c);
     a.next_src = c->packed[c->cur ^ 1];
     a.next_off = c->p.rank * c->slot_bodies;
     a.maxseg = c->plan_full.maxseg;
@@ -477,7 +477,7 @@ int get_cached(int n, bool host_buffers, Cached** out, int variant = NBODY_VARIA
         k.var = find_variant(variant == NBODY_VARIANT_AUTO ? auto_variant(n, n) : variant);
         if (!k.var) { g_cache.erase(std::make_pair(std::make_pair(dev, n), variant)); return fail(NBODY_E_INVALID, "unknown kernel variant %d", variant); }
         k.n_pad = round_up(n, kSlotAlign);
-        int rc = make_plan(k.var, prop.multiProcessorCount, 0, n, k.n_pad / k.var->UJ, &k.plan);
+        int rc = make_plan(k.var, prop.multiProcessorCount, 0, n, round_up(n, k.var->UJ) / k.var->UJ, &k.plan);   // units up to the last body (units_in_use)
         if (rc) { k = Cached(); return rc; }
         cudaError_t e = cudaMalloc(&k.packed, (size_t)k.n_pad * sizeof(float4));
         if (e == cudaSuccess) e = cudaMalloc(&k.partial, k.plan.partial_bytes);
@@ -503,7 +503,7 @@ int enqueue_one_step(Cached* k, float4* dX, float4* dA, float4* dV, int n, float
     a.X = dX; a.V = dV; a.A = dA;
     a.n_targets = n;
     a.src = k->packed;
-    a.ra_begin = 0; a.ra_count = k->n_pad / k->var->UJ;
+    a.ra_begin = 0; a.ra_count = round_up(n, k->var->UJ) / k->var->UJ;
     a.partial = k->partial; a.counters = k->counters; a.maxseg = k->plan.maxseg;
     a.eps2 = eps2; a.dt = dt; a.integ_f64 = f64; a.dt64 = dt64; a.va_f3 = va_f3;
     return launch_force(k->var, k->plan, a, st);
@@ -612,7 +612,7 @@ int get_cached_multi(int n, int variant, CachedMulti** out)
             }
             if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&m.st, cudaStreamNonBlocking);
         }
-        if (e == cudaSuccess) rc = make_plan(var, prop.multiProcessorCount, 0, m.n_targets, k.n_pad / var->UJ, &m.plan);
+        if (e == cudaSuccess) rc = make_plan(var, prop.multiProcessorCount, 0, m.n_targets, round_up(n, var->UJ) / var->UJ, &m.plan);
         if (!rc && e == cudaSuccess) e = cudaMalloc(&m.packed, (size_t)k.n_pad * sizeof(float4));
         if (!rc && e == cudaSuccess) e = cudaMalloc(&m.partial, m.plan.partial_bytes);
         if (!rc && e == cudaSuccess) e = cudaMalloc(&m.counters, (size_t)m.plan.num_counters * sizeof(unsigned));
@@ -655,7 +655,7 @@ int one_step_multi(CachedMulti* k, float4* dX, void* dA, void* dV, int n, float 
         a.A = reinterpret_cast<float4*>(static_cast<char*>(dA) + va_stride * (size_t)m.t_begin);
         a.n_targets = m.n_targets;
         a.src = m.packed;
-        a.ra_begin = 0; a.ra_count = k->n_pad / k->var->UJ;
+        a.ra_begin = 0; a.ra_count = round_up(n, k->var->UJ) / k->var->UJ;
         a.partial = m.partial; a.counters = m.counters; a.maxseg = m.plan.maxseg;
         a.eps2 = eps2; a.dt = dt; a.integ_f64 = integ; a.va_f3 = va_f3;
         rc = launch_force(k->var, m.plan, a, m.st);
