@@ -112,6 +112,8 @@ const Variant kVariants[] = {
     MVARIANT(111, 8, 256, 64, 2, 6, 1),
     MVARIANT(112, 6, 256, 128, 2, 18, 1),
     MVARIANT(113, 6, 256, 64, 2, 18, 1),
+    MVARIANT(116, 8, 256, 32, 2, 6, 1),      // 32-body units: 8 k .. 11 k bodies, where a CTA has only 3 - 5 larger units
+    MVARIANT(117, 6, 256, 32, 2, 18, 1),
     // thread-block-cluster exemplars (opt-in; measured neutral / slower, profiles/r1_ncu_cluster_evidence.md):
     // m1 = TMA multicast of source units, m2 = j-split with DSMEM reduction
     CVARIANT(60, 6, 256, 256, 2, 1, 1, 2, 1),
@@ -224,7 +226,7 @@ int auto_variant(int n_targets, int n_sources, bool deterministic = false)
 int mid_variant(int n_targets, int n_sources, int sms)
 {
     struct Cand { int id, T, UJ; };
-    static const Cand cands[] = {{90, 6, 256}, {112, 6, 128}, {113, 6, 64}, {93, 8, 256}, {110, 8, 128}, {111, 8, 64}};
+    static const Cand cands[] = {{90, 6, 256}, {112, 6, 128}, {113, 6, 64}, {117, 6, 32}, {93, 8, 256}, {110, 8, 128}, {111, 8, 64}, {116, 8, 32}};
     if (sms <= 0) {
         int dev = 0;
         sms = 148;

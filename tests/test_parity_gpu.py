@@ -226,7 +226,8 @@ def test_sharded_contexts_on_one_gpu_match_unsharded(cuda, nb, oracle, world):
             s.close()
     x = np.concatenate([p[0] for p in parts]); v = np.concatenate([p[1] for p in parts]); a = np.concatenate([p[2] for p in parts])
     assert len(x) == n
-    assert oracle.norm_rel_err(a, ar) <= 3e-6 and oracle.norm_rel_err(x, xr) <= 1e-6 and oracle.norm_rel_err(v, vr) <= 3e-6
+    # (the sharded-vs-one-GPU bounds of SURVEY 8c: 1e-5 on a and v, 1e-6 on x; three steps, measured 2e-6 .. 3.1e-6)
+    assert oracle.norm_rel_err(a, ar) <= 1e-5 and oracle.norm_rel_err(x, xr) <= 1e-6 and oracle.norm_rel_err(v, vr) <= 1e-5
 
 
 def _problem_counts(binary, steps):
