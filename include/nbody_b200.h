@@ -219,6 +219,23 @@ int nbody_set_devices(const int* devices, int n);
 /* Releases the per-(device, N) scratch the calls above keep between calls. */
 void nbody_release_cached(void);
 
+/* One in-place step on DEVICE float4 arrays like nbody_step_inplace_f4, but ALLOCATING NOTHING: no cudaMalloc,
+ * cudaFree or allocating library routine on any call, first or later.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  The step kernel's scratch (packed snapshot of the sources,
+ * partial sums of split target tiles, tile counters) is a static 8 MiB device array inside the library
+ * (csrc/nbody_noalloc.inl), which every GPU that loads the library holds until the process exits.
+ *   - n <= nbody_noalloc_max_bodies() = 16 384; larger n is refused with NBODY_E_INVALID (use the call above).
+ *   - the work is ENQUEUED on `stream` (a cudaStream_t passed as void*, NULL = the legacy default stream) on the
+ *     current device; the call does not synchronise.
+ *   - all calls on one GPU share the array: calls that can overlap on the GPU (different streams, threads,
+ *     graphs replayed side by side) race on it -- serialise them.  Nothing is assumed about the array's contents
+ *     between calls (the counters are cleared on `stream` before each step).
+ *   - always the stream-K kernel: from 8 192 bodies up the same kernel shape as nbody_step_inplace_f4 (identical
+ *     results); below, that call uses its small-N kernels and the two agree to summation rounding (<= 1e-5). */
+int nbody_step_inplace_noalloc_f4(float* d_bodies4, float* d_accel4, float* d_vel4, int n, float eps2, float dt, void* stream);
+int nbody_noalloc_max_bodies(void);
+
 /* ---- headless frame: the reference's per-step OpenGL draw as CUDA --------
  * Shader arithmetic of TestProject/simulation_visualization.cpp:15-56 (weight,
  * NDC position, mix(green, red, weight)), 1-pixel points with the depth test

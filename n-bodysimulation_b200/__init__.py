@@ -87,6 +87,8 @@ SIGNATURES = {
     "nbody_set_devices": (C.c_int, [C.POINTER(C.c_int), C.c_int]),
     "nbody_group_info": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "nbody_step_inplace_f4": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_float, C.c_float]),
+    "nbody_step_inplace_noalloc_f4": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_float, C.c_float, _vp]),
+    "nbody_noalloc_max_bodies": (C.c_int, []),
     "nbody_step_host_f3": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_double, C.c_double]),
     "nbody_step_opts_default": (C.c_int, [C.POINTER(NBodyStepOpts)]),
     "nbody_step_inplace_opts": (C.c_int, [_vp, _vp, _vp, C.c_int, C.POINTER(NBodyStepOpts)]),
@@ -190,6 +192,15 @@ def simulate(d_bodies, d_accelerations, d_velocity, N: int) -> None:
     """TestProject/kernel.cuh:2 -- DEVICE float4 arrays (torch CUDA tensors or raw
     pointers), one step in place, synchronous."""
     _check(lib.nbody_step_inplace_f4(_ptr(d_bodies), _ptr(d_accelerations), _ptr(d_velocity), int(N), _eps2, _dt))
+
+
+def simulate_noalloc(d_bodies, d_accelerations, d_velocity, N: int, stream=None) -> None:
+    """nbody_step_inplace_noalloc_f4: the same step as simulate() for N <= nbody_noalloc_max_bodies(), enqueued on
+    `stream` (a cudaStream_t as int, None = the legacy default stream) without any allocation: the kernel's
+    scratch is a static device array of the library.  Not synchronised; overlapping calls race (see the header).
+    No counterpart in the reference."""
+    _check(lib.nbody_step_inplace_noalloc_f4(_ptr(d_bodies), _ptr(d_accelerations), _ptr(d_velocity), int(N), _eps2, _dt,
+                                             C.c_void_p(stream) if stream else None))
 
 
 def simulate_host_f3(bodies: np.ndarray, accelerations: np.ndarray, velocity: np.ndarray, N: int,

@@ -784,3 +784,4 @@ int nbody_owned_range(nbody_ctx* c, int* begin, int* count)
 #include "nbody_render.inl"
 #include "nbody_records.inl"
 #include "nbody_group.inl"
+#include "nbody_noalloc.inl"
