@@ -669,7 +669,7 @@ def run_ours(args):
                     ms = s.elapsed_ms() / st
                     small_n.append({"n_bodies": nn, "steps": st, "us_per_step": round(ms * 1e3, 2), "value": round(nn * float(nn) / ms / 1e6, 1),
                                     "pct_fp32_peak": round(100 * FLOP_PER_INTERACTION * nn * float(nn) / ms / 1e9 / peak_tflops, 2),
-                                    "kernel": s.info()["variant_name"], "split_tiles_finished_by": "all their CTAs (cooperative launch)" if s.info()["spread_fixup"] else "the last CTA to arrive",
+                                    "kernel": s.info()["variant_name"], "split_tiles_finished_by": "no tile is split (row-split kernel: whole target tiles per CTA)" if s.info()["variant_name"].startswith("R_") else "all their CTAs (cooperative launch)" if s.info()["spread_fixup"] else "the last CTA to arrive",
                                     "timing": "nbody_step(ctx, steps), one CUDA-event pair around the loop"})
         if world == 1:   # the same kernel with ONE running sum per target (nbody_params.summation = NBODY_SUM_SINGLE): speed vs accuracy
             import numpy as np

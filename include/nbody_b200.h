@@ -231,8 +231,8 @@ void nbody_release_cached(void);
  *   - all calls on one GPU share the array: calls that can overlap on the GPU (different streams, threads,
  *     graphs replayed side by side) race on it -- serialise them.  Nothing is assumed about the array's contents
  *     between calls (the counters are cleared on `stream` before each step).
- *   - always the stream-K kernel: from 8 192 bodies up the same kernel shape as nbody_step_inplace_f4 (identical
- *     results); below, that call uses its small-N kernels and the two agree to summation rounding (<= 1e-5). */
+ *   - always the stream-K kernel (the one that needs the scratch); nbody_step_inplace_f4 picks its kernel family by
+ *     size, so the two agree to summation rounding (accelerations <= 1e-5, positions <= 1e-6), not bit for bit. */
 int nbody_step_inplace_noalloc_f4(float* d_bodies4, float* d_accel4, float* d_vel4, int n, float eps2, float dt, void* stream);
 int nbody_noalloc_max_bodies(void);
 

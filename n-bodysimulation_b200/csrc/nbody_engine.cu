@@ -67,13 +67,16 @@ struct Variant {
     void (*kernel_spread)(const ForceArgs) = nullptr;          // mid-size N: split tiles finished by all their CTAs
     void (*kernel_spread_single)(const ForceArgs) = nullptr;   // (force_kernel's SPREAD; cooperative launch)
     int small = 0;   // 1: small_kernel (T = targets per CTA, sources split over the CTA's threads, shuffle reduction)
-    size_t smem(bool single = false) const { return small ? 0 : (size_t)kStages * UJ * 16 + 16 * kStages + 16 + (cmode == 2 ? (size_t)TI() * 16 : 0) + fold_bytes(T, NT, packed != 0, !single); }
+                     // 2: rowsplit_kernel (T x H targets per CTA, sources split over the warps and their sub-groups)
+    int H = 0;       // rowsplit_kernel: lanes of a warp that hold different targets (4, 8, 16 or 32)
+    void (*kernel_trim)(const ForceArgs) = nullptr;   // rowsplit_kernel that skips the padding of a ragged last unit
+    size_t smem(bool single = false) const { return small == 1 ? 0 : small == 2 ? (size_t)kStages * UJ * 16 + 16 * kStages + 16 : (size_t)kStages * UJ * 16 + 16 * kStages + 16 + (cmode == 2 ? (size_t)TI() * 16 : 0) + fold_bytes(T, NT, packed != 0, !single); }
     void (*entry(bool single, bool spread = false) const)(const ForceArgs)
     {
         if (spread && kernel_spread) return single && kernel_spread_single ? kernel_spread_single : kernel_spread;
         return single && kernel_single ? kernel_single : kernel;
     }
-    int TI() const { return small ? T : T * NT; }
+    int TI() const { return small == 1 ? T : small == 2 ? T * H : T * NT; }
     int TS() const { return cmode == 1 ? TI() * cs : TI(); }          // targets per worker tile
 };
 
@@ -88,6 +91,9 @@ struct Variant {
 
 #define SVARIANT(id, TT, NT, UN) \
     { id, "S_TT" #TT "_NT" #NT "_U" #UN, TT, NT, 64, UN, 1, 1, 1, 0, small_kernel<TT, NT, UN>, nullptr, nullptr, nullptr, 1 }
+// row-split family (mid-size N that divides evenly over the SMs): T x H targets per CTA, no scratch
+#define RVARIANT(id, T, H, UJ, UN, ORD) \
+    { id, "R_T" #T "_H" #H "_NT256_UJ" #UJ "_U" #UN "_" #ORD, T, 256, UJ, UN, 1, 1, 1, 0, rowsplit_kernel<T, H, 256, UJ, UN, ORD>, nullptr, nullptr, nullptr, 2, H, rowsplit_kernel<T, H, 256, UJ, UN, ORD, 1> }
 // packed: 0 = scalar FFMA path (kept as the with/without evidence of the f32x2 choice), 1 = FADD2/FMUL2/FFMA2,
 // 5 / 6 / 7 / 8 = the same packed arithmetic in another source order (bit-identical results; ptxas' register
 // allocation differs by a few per cent, see tuned_large_variant).
@@ -121,6 +127,23 @@ const Variant kVariants[] = {
     // small-N family: j-split inside the CTA, warp-shuffle reduction, no scratch
     SVARIANT(82, 4, 128, 2),
     SVARIANT(85, 2, 128, 4),
+    // row-split family: whole target tiles per CTA, every CTA streams all sources (mid_variant picks them when
+    // ceil(N / tile) fills the SMs evenly)
+    RVARIANT(150, 5, 16, 1024, 4, 0),
+    RVARIANT(151, 6, 16, 1024, 4, 0),
+    RVARIANT(152, 7, 16, 1024, 4, 0),        // N = 16 384 (BASELINE config 2): 147 CTAs x 112 targets
+    RVARIANT(153, 8, 16, 1024, 4, 0),
+    RVARIANT(160, 5, 8, 1024, 4, 0),
+    RVARIANT(161, 6, 8, 1024, 4, 0),
+    RVARIANT(162, 7, 8, 1024, 4, 0),
+    RVARIANT(163, 8, 8, 1024, 4, 0),
+    RVARIANT(165, 6, 4, 1024, 4, 0),
+    RVARIANT(166, 7, 4, 1024, 4, 0),
+    RVARIANT(167, 8, 4, 1024, 4, 0),
+    RVARIANT(170, 5, 32, 1024, 4, 0),
+    RVARIANT(171, 6, 32, 1024, 4, 0),
+    RVARIANT(172, 7, 32, 1024, 4, 0),
+    RVARIANT(173, 8, 32, 1024, 4, 0),
 #ifdef NBODY_SWEEP_VARIANTS
     VARIANT(45, 6, 256, 256, 2, 1, 1),       // x,y,z source order: 2 % slower than the orders above once the sums are folded
     VARIANT(46, 6, 256, 256, 2, 5, 1),
@@ -164,6 +187,11 @@ const Variant kVariants[] = {
     CVARIANT(66, 2, 256, 256, 8, 1, 3, 2, 2),
     CVARIANT(67, 2, 256, 256, 8, 1, 3, 4, 2),
     CVARIANT(70, 6, 256, 256, 2, 1, 1, 8, 2),
+    RVARIANT(180, 7, 16, 512, 4, 0),         // unit size / unroll evidence of the row-split family (profiles/r2_rowsplit.txt)
+    RVARIANT(181, 7, 16, 512, 2, 0),
+    RVARIANT(182, 7, 16, 256, 2, 0),
+    RVARIANT(183, 7, 16, 512, 8, 0),
+    RVARIANT(184, 7, 16, 1024, 4, 5),
     SVARIANT(80, 8, 128, 2),
     SVARIANT(81, 8, 256, 2),
     SVARIANT(83, 16, 256, 1),
@@ -199,9 +227,51 @@ int env_int(const char* name, int dflt)
 // CTA / CTAs per wave (+8 % at 6 144, -7 % at 7 680), so the rule stays simple.
 // NBODY_SMALL_BELOW in the environment moves it (tuning switch).
 const int g_small_below = env_int("NBODY_SMALL_BELOW", 8192);
+// Row-split family (rowsplit_kernel): whole target tiles of T x H bodies per CTA, one wave.  Its time is one CTA's:
+// tile x sources at the shape's measured rate + a fixed 3.5 us (launch, prologue, reduction); it wins where
+// ceil(N / tile) fills the SMs evenly, because nothing crosses CTAs (no partial sums through global memory).
+// Rates: G interactions / s on 148 SMs at N = 148 x tile (tools/experiment_rowsplit.sh, profiles/r2_rowsplit.txt).
+int round_up(int v, int m) { return (v + m - 1) / m * m; }
+struct RowCand { int id, T, H; double rate; };
+const RowCand kRowCands[] = {
+    {165, 6, 4, 2500.}, {166, 7, 4, 2500.}, {167, 8, 4, 2500.},
+    {160, 5, 8, 2500.}, {161, 6, 8, 2640.}, {162, 7, 8, 2620.}, {163, 8, 8, 2645.},
+    {150, 5, 16, 2550.}, {151, 6, 16, 2600.}, {152, 7, 16, 2690.}, {153, 8, 16, 2600.},
+    {170, 5, 32, 2625.}, {171, 6, 32, 2640.}, {172, 7, 32, 2680.}, {173, 8, 32, 2645.},
+};
+const bool g_rowsplit = getenv("NBODY_NO_ROWSPLIT") == nullptr;   // with / without switch of the experiments
+int row_variant(int n, int sms, double* t_us)
+{
+    int best = 0;
+    *t_us = 1e300;
+    for (const RowCand& c : kRowCands) {
+        const int tile = c.T * c.H;
+        if ((n + tile - 1) / tile > sms) continue;   // one wave only: a second wave of whole tiles loses to stream-K
+        const int quantum = 2 * (32 / c.H) * 8 * 4;   // bodies per round of the CTA's source split (unroll 4)
+        const double t = (double)tile * (double)round_up(n, quantum) * 148.0 / (c.rate * 1e3) + 3.5;
+        if (t < *t_us) { *t_us = t; best = c.id; }
+    }
+    return best;
+}
+
 int static_variant(int n_targets, int n_sources, int sms, bool* measured)
 {
     *measured = false;
+    if (g_rowsplit && n_targets == n_sources && n_sources >= 2048 && n_sources < 65536) {
+        // unsharded mid-size system: row-split where its whole tiles fill the SMs well enough to beat the others'
+        // measured times (small-N family: N^2 / 1.9e6 + 3.2 us; stream-K kernels: 1.04 N^2 / 2.69e6 + 12 us on 148 SMs;
+        // both a little optimistic for the others, so a tie goes to them)
+        if (sms <= 0) {
+            int dev = 0;
+            sms = 148;
+            if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        }
+        double t_row = 0.0;
+        const int id = row_variant(n_sources, sms, &t_row);
+        const double n2 = (double)n_sources * (double)n_sources;
+        const double t_other = n_sources < g_small_below ? n2 / 1.9e6 + 3.2 : 1.04 * n2 / (2.69e6 * sms / 148.0) + 12.0;
+        if (id && t_row < 0.99 * t_other) return id;
+    }
     if (n_sources < g_small_below) {     // a step is < 50 us: latency decides -> small-N family
         if (n_sources < 3072) return 85; // 2 targets / CTA, sources split over 128 threads, shuffle reduction
         return 82;                       // 4 targets / CTA
@@ -248,7 +318,6 @@ int mid_variant(int n_targets, int n_sources, int sms)
     return best;
 }
 
-int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
 // The kernels take rsqrt.approx.ftz of (r^2 + eps2)^3: for the self term and the zero-mass padding r = 0, so a
 // subnormal eps2^3 is flushed to 0, rsqrt gives +inf and 0 * inf = NaN in every acceleration.  (The reference
@@ -281,10 +350,14 @@ int make_plan(const Variant* v, int sm_count, int grid_override, int n_targets, 
 {
     Plan pl;
     pl.single = single && v->kernel_single;
-    if (v->small) {   // one CTA per T targets, every CTA visits all J units: nothing to cut, no scratch
+    if (v->small) {   // one CTA per tile of targets, every CTA visits all J units: nothing to cut, no scratch
         (void)sm_count; (void)grid_override; (void)J;
         pl.occ = 1;
-        pl.num_itiles = (n_targets + v->T - 1) / v->T;
+        if (v->small == 2) {
+            CU(cudaFuncSetAttribute(v->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v->smem()));
+            CU(cudaFuncSetAttribute(v->kernel_trim, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v->smem()));
+        }
+        pl.num_itiles = (n_targets + v->TI() - 1) / v->TI();
         pl.grid = pl.num_itiles;
         pl.maxseg = 1; pl.num_counters = 1; pl.partial_bytes = sizeof(float4);
         *out = pl;
@@ -360,6 +433,8 @@ int launch_force(const Variant* v, const Plan& pl, const ForceArgs& args_in, cud
         cfg.gridDim = dim3(pl.grid); cfg.blockDim = dim3(v->NT); cfg.dynamicSmemBytes = v->smem(pl.single); cfg.stream = st;
         cfg.attrs = at; cfg.numAttrs = 1;
         CU(cudaLaunchKernelEx(&cfg, v->entry(pl.single), args));
+    } else if (v->small == 2 && args.last_unit_bodies > 0 && args.rb_count == 0) {
+        v->kernel_trim<<<pl.grid, v->NT, v->smem(), st>>>(args);   // ragged last unit: its padding is not visited
     } else {
         v->entry(pl.single)<<<pl.grid, v->NT, v->smem(pl.single), st>>>(args);
     }
@@ -542,6 +617,13 @@ int units_in_use(const nbody_ctx* c)
     return ((c->p.world - 1) * c->slot_bodies + round_up(last, UJ)) / UJ;
 }
 
+// real bodies in the last of those units (0 = the unit is full)
+int last_unit_fill(const nbody_ctx* c)
+{
+    const int last = c->n - (c->p.world - 1) * c->per;
+    return last % c->var->UJ;
+}
+
 // ... and of this shard's own slot (the last shard's slot ends early)
 int units_own_in_use(const nbody_ctx* c)
 {
@@ -614,9 +696,10 @@ int nbody_variant_info(int id, char* buf, size_t buflen)
     const Variant* v = find_variant(id);
     if (buf && buflen) buf[0] = 0;
     if (v && buf && buflen) {
-        char cl[96] = "";
+        char cl[192] = "";
         if (v->cs > 1) snprintf(cl, sizeof cl, ", clusters of %d CTAs (%s)", v->cs, v->cmode == 1 ? "TMA multicast of source units" : "j-split, DSMEM reduction");
-        if (v->small) snprintf(cl, sizeof cl, ", small-N family: %d targets/CTA, sources split over the CTA, warp-shuffle reduction", v->T);
+        if (v->small == 1) snprintf(cl, sizeof cl, ", small-N family: %d targets/CTA, sources split over the CTA, warp-shuffle reduction", v->T);
+        if (v->small == 2) snprintf(cl, sizeof cl, ", row-split family: %d targets/CTA (%d lanes x T), every CTA streams all sources, split %d ways over its warps", v->TI(), v->H, (32 / v->H) * (v->NT / 32));
         snprintf(buf, buflen, "%s: %d targets/thread, %d threads/CTA, %d sources/tile, unroll %d pairs, %s FP32, min %d CTAs/SM, %zu B smem%s",
                  v->name, v->T, v->NT, v->UJ, v->unroll,
                  v->packed == 0 ? "scalar" : v->packed == 1 ? "packed f32x2" : v->packed == 5 ? "packed f32x2, targets reversed" : v->packed == 6 ? "packed f32x2, target-outer order" : v->packed == 18 ? "packed f32x2, x,z,y order" : "packed f32x2, z-first order",

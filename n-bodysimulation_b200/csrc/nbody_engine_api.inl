@@ -21,6 +21,7 @@ int enqueue_full_step(nbody_ctx* c, cudaStream_t st)
     ForceArgs a = base_args(c);
     a.ra_begin = 0; a.ra_count = units_in_use(c);
     a.rb_begin = 0; a.rb_count = 0;
+    a.last_unit_bodies = last_unit_fill(c);
     a.next_src = c->packed[c->cur ^ 1];
     a.next_off = c->p.rank * c->slot_bodies;
     a.maxseg = c->plan_full.maxseg;
@@ -370,6 +371,7 @@ int nbody_shard_step_fused_async(nbody_ctx* c, void* stream)
     if (c->peers_attached != c->p.world - 1) return fail(NBODY_E_STATE, "%d of %d peers attached", c->peers_attached, c->p.world - 1);
     ForceArgs a = base_args(c);
     a.ra_begin = 0; a.ra_count = units_in_use(c);
+    a.last_unit_bodies = last_unit_fill(c);
     a.next_src = c->packed[c->cur ^ 1];
     a.next_off = c->p.rank * c->slot_bodies;
     a.maxseg = c->plan_full.maxseg;
@@ -504,6 +506,7 @@ int enqueue_one_step(Cached* k, float4* dX, float4* dA, float4* dV, int n, float
     a.n_targets = n;
     a.src = k->packed;
     a.ra_begin = 0; a.ra_count = round_up(n, k->var->UJ) / k->var->UJ;
+    a.last_unit_bodies = n % k->var->UJ;
     a.partial = k->partial; a.counters = k->counters; a.maxseg = k->plan.maxseg;
     a.eps2 = eps2; a.dt = dt; a.integ_f64 = f64; a.dt64 = dt64; a.va_f3 = va_f3;
     return launch_force(k->var, k->plan, a, st);
@@ -656,6 +659,7 @@ int one_step_multi(CachedMulti* k, float4* dX, void* dA, void* dV, int n, float 
         a.n_targets = m.n_targets;
         a.src = m.packed;
         a.ra_begin = 0; a.ra_count = round_up(n, k->var->UJ) / k->var->UJ;
+        a.last_unit_bodies = n % k->var->UJ;
         a.partial = m.partial; a.counters = m.counters; a.maxseg = m.plan.maxseg;
         a.eps2 = eps2; a.dt = dt; a.integ_f64 = integ; a.va_f3 = va_f3;
         rc = launch_force(k->var, m.plan, a, m.st);

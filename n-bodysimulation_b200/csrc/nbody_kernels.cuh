@@ -73,6 +73,8 @@ struct ForceArgs {
     int integ_f64;        // 0: float integrator (kernel.cu:116-124 / validation.cpp:43-49), 1: double (headless
                           // flavour), 2: mixed (reduction flavours, kernel.cu:455-463: double half-kick, float drift)
     int va_f3;            // 1: V and A are packed float3 arrays (FLOAT_3 build of the reference, main.cpp:233-269)
+    int last_unit_bodies; // real bodies in the last unit of range A (0 = all of it): the zero-mass padding behind them
+                          // need not be visited (rowsplit_kernel, whose units are 1 024 bodies; others ignore it)
     double dt64;
     // optional: CTA 0 records {clock64, globaltimer} at entry and exit -> SM clock actually run at;
     // clk[4] += ns its thread 0 spent in the cross-GPU flag wait, clk[5] = the longest single wait, clk[6] = waits
@@ -740,6 +742,154 @@ __global__ void __launch_bounds__(NT) small_kernel(const ForceArgs a)
         const int gi = g0 + lane;
         integrate_one(a, gi, lane < TT && gi < a.n_targets, fx, fy, fz, lane);
     }
+}
+
+// ---- row-split kernel: mid-size N whose targets divide evenly over the SMs -----------------------------
+// At N = 16 384 the stream-K cut leaves every target tile shared by ~18 CTAs: each writes its partial sums to
+// global memory, waits for the others and reads 18 of them back (profiles/r2_ncu_full_16k_spread_raw.csv; about
+// a tenth of a 112 us step is prologue + that round trip).  When ceil(N / 148) is close to a shape a CTA can hold
+// -- T x H targets: H = 4, 8, 16 or 32 lanes of every warp hold T targets each -- nothing needs to cross CTAs at all:
+// CTA b owns targets [b TI, (b + 1) TI) and streams ALL source units through the same TMA ring as force_kernel;
+// the source pairs of a unit are split 32 / H x NT / 32 ways over the sub-groups of a warp and the warps (the
+// north-star's j-split), every thread keeping its T targets in registers for the whole kernel, and the partial
+// sums meet once at the end: shfl.xor across the sub-groups of a warp, then shared memory across the warps in
+// fixed order (deterministic).  One launch, no scratch, no atomics, no cooperative launch.  Each accumulator sees
+// N / (2 x split) additions (512 at N = 16 384), so no second summation level is needed below 64 k sources.
+// Same ForceArgs as force_kernel (both source ranges, two-phase accumulators, peer stores); no in-kernel barrier.
+// TRIM 1: the zero-mass padding behind the last real body of the last unit is skipped (ForceArgs.last_unit_bodies); a
+// separate instantiation, launched only when N is not a multiple of the unit: with the variable trip count in the
+// code ptxas allocates the common loop differently (N = 16 384: 104.8 us instead of 103.6).  Same sums either way.
+template <int T, int H, int NT, int UJ, int UNROLL, int ORD = 0, int TRIM = 0>
+__global__ void __launch_bounds__(NT, 1) rowsplit_kernel(const ForceArgs a)
+{
+    constexpr int SUB = 32 / H, NW = NT / 32, SPLIT = SUB * NW, TI = T * H;
+    constexpr int PER = (UJ / 2) / SPLIT;                 // pairs of one unit per thread
+    constexpr uint32_t kStageBytes = UJ * 16;
+    static_assert(H == 4 || H == 8 || H == 16 || H == 32, "lanes per target group");
+    static_assert(PER >= UNROLL && PER % UNROLL == 0, "the unit's pairs must divide over the split and the unroll");
+    static_assert(TI % 2 == 0 && TI <= NT, "one finishing thread per target, pairs stay inside the tile");
+    static_assert((size_t)NW * 3 * TI * sizeof(float) <= (size_t)kStages * kStageBytes, "the reduction area aliases the ring");
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const uint32_t smem_base = smem_u32(smem_raw);
+    const uint32_t bar_full = smem_base + kStages * kStageBytes;
+    const uint32_t bar_empty = bar_full + 8 * kStages;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int hl = lane % H, myq = wid * SUB + lane / H;   // target column, index in the source split
+    if (a.clk && blockIdx.x == 0 && tid == 0) { a.clk[0] = clock64(); a.clk[1] = globaltimer_ns(); }
+    const int J = a.ra_count + a.rb_count;
+    // pairs per thread of the last unit: the zero-mass padding behind the last real body is skipped (whole unrolls)
+    const int last_per = (TRIM && a.last_unit_bodies > 0 && a.rb_count == 0)
+                             ? min(PER, (a.last_unit_bodies + 2 * SPLIT * UNROLL - 1) / (2 * SPLIT * UNROLL) * UNROLL) : PER;
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < kStages; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, NW); }
+        mbar_fence_init();
+    }
+    __syncthreads();
+    int pj = 0, kf = 0;   // producer (thread 0): next source unit, fetches issued
+    auto issue = [&]() {
+        if (pj >= J) return;
+        const int s = kf & (kStages - 1), n = kf / kStages;
+        if (n > 0) mbar_wait(bar_empty + 8 * s, (n - 1) & 1);
+        const int ju = pj < a.ra_count ? a.ra_begin + pj : a.rb_begin + (pj - a.ra_count);
+        mbar_arrive_expect_tx(bar_full + 8 * s, kStageBytes);
+        tma_bulk_g2s(smem_base + s * kStageBytes, a.src + (size_t)ju * UJ, kStageBytes, bar_full + 8 * s);
+        ++pj; ++kf;
+    };
+    if (tid == 0)
+        for (int i = 0; i < kLookahead; ++i) issue();
+
+    const int g0 = blockIdx.x * TI;
+    u64 nx[T], ny[T], nz[T], ax[T], ay[T], az[T];
+#pragma unroll
+    for (int t = 0; t < T; ++t) {
+        const int gi = g0 + hl + t * H;
+        float4 xi = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (gi < a.n_targets) xi = a.X[gi];
+        nx[t] = pack2(-xi.x, -xi.x); ny[t] = pack2(-xi.y, -xi.y); nz[t] = pack2(-xi.z, -xi.z);
+        ax[t] = 0ull; ay[t] = 0ull; az[t] = 0ull;
+    }
+    const u64 eps2p = pack2(a.eps2, a.eps2);
+    // one source unit against this thread's targets; `per` = pairs per thread (a constant for all units but the last,
+    // so the body is instantiated twice and the common case keeps its compile-time trip count)
+    auto consume = [&](const int k, const int per) {
+        if (tid == 0) issue();
+        const int s = k & (kStages - 1);
+        mbar_wait(bar_full + 8 * s, (k / kStages) & 1);
+        const ulonglong2* sp = reinterpret_cast<const ulonglong2*>(smem_raw + s * kStageBytes) + 2 * myq;
+#pragma unroll 1
+        for (int i = 0; i < per; i += UNROLL) {
+#pragma unroll
+            for (int q = 0; q < UNROLL; ++q) {
+                const ulonglong2 xy = sp[2 * SPLIT * (i + q)], zm = sp[2 * SPLIT * (i + q) + 1];   // (x0,x1)(y0,y1) | (z0,z1)(m0,m1)
+#pragma unroll
+                for (int t = 0; t < T; ++t) {
+                    u64 dx, dy, dz;
+                    if (ORD == 1) { dz = add2(zm.x, nz[t]); dy = add2(xy.y, ny[t]); dx = add2(xy.x, nx[t]); }
+                    else if (ORD == 5) { dx = add2(xy.x, nx[t]); dz = add2(zm.x, nz[t]); dy = add2(xy.y, ny[t]); }
+                    else { dx = add2(xy.x, nx[t]); dy = add2(xy.y, ny[t]); dz = add2(zm.x, nz[t]); }
+                    u64 r2 = fma2(dx, dx, eps2p);
+                    r2 = fma2(dy, dy, r2);
+                    r2 = fma2(dz, dz, r2);
+                    const u64 d3 = mul2(mul2(r2, r2), r2);      // (r^2+eps2)^3, as kernel.cu:20
+                    float lo, hi;
+                    unpack2(d3, lo, hi);
+                    const u64 sc = mul2(pack2(rsqrt_mufu(lo), rsqrt_mufu(hi)), zm.y);
+                    if (ORD == 1) { az[t] = fma2(dz, sc, az[t]); ay[t] = fma2(dy, sc, ay[t]); ax[t] = fma2(dx, sc, ax[t]); }
+                    else if (ORD == 5) { ax[t] = fma2(dx, sc, ax[t]); az[t] = fma2(dz, sc, az[t]); ay[t] = fma2(dy, sc, ay[t]); }
+                    else { ax[t] = fma2(dx, sc, ax[t]); ay[t] = fma2(dy, sc, ay[t]); az[t] = fma2(dz, sc, az[t]); }
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_empty + 8 * s);
+    };
+    if (TRIM) {
+#pragma unroll 1
+        for (int k = 0; k < J - 1; ++k) consume(k, PER);
+        consume(J - 1, last_per);
+    } else {
+#pragma unroll 1
+        for (int k = 0; k < J; ++k) consume(k, PER);
+    }
+    // ---- the SPLIT partial sums of every target: sub-groups of a warp (shfl.xor), then warps (shared memory) ----
+    float f[T][3];
+#pragma unroll
+    for (int t = 0; t < T; ++t) {
+        float lo, hi;
+        unpack2(ax[t], lo, hi); f[t][0] = __fadd_rn(lo, hi);
+        unpack2(ay[t], lo, hi); f[t][1] = __fadd_rn(lo, hi);
+        unpack2(az[t], lo, hi); f[t][2] = __fadd_rn(lo, hi);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+#pragma unroll
+            for (int m = H; m < 32; m <<= 1) f[t][c] = __fadd_rn(f[t][c], __shfl_xor_sync(0xffffffffu, f[t][c], m));
+        }
+    }
+    __syncthreads();   // every warp has consumed every unit: the ring is free
+    float* s_red = reinterpret_cast<float*>(smem_raw);   // [NW][3][TI]
+    if (lane < H) {
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) s_red[(wid * 3 + c) * TI + hl + t * H] = f[t][c];
+        }
+    }
+    __syncthreads();
+    if (tid < ((TI + 31) & ~31)) {   // whole warps: integrate_one exchanges pair halves by shuffle
+        float fx = 0.f, fy = 0.f, fz = 0.f;
+        if (tid < TI) {
+#pragma unroll
+            for (int w = 0; w < NW; ++w) {
+                fx = __fadd_rn(fx, s_red[(w * 3 + 0) * TI + tid]);
+                fy = __fadd_rn(fy, s_red[(w * 3 + 1) * TI + tid]);
+                fz = __fadd_rn(fz, s_red[(w * 3 + 2) * TI + tid]);
+            }
+        }
+        const int gi = g0 + tid;
+        integrate_one(a, gi, tid < TI && gi < a.n_targets, fx, fy, fz, lane);
+    }
+    if (a.clk && blockIdx.x == 0 && tid == 0) { a.clk[2] = clock64(); a.clk[3] = globaltimer_ns(); }
 }
 
 // ---- AoS float4 -> packed pair layout (pre-pass of the in-place API and of upload) ----

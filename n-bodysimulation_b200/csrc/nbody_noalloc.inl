@@ -81,8 +81,8 @@ int nbody_step_inplace_noalloc_f4(float* d_bodies4, float* d_accel4, float* d_ve
     int sms = 0;
     int rc = noalloc_scratch(&base, &sms);
     if (rc) return rc;
-    // always the stream-K force kernel (the one with scratch): the shape nbody_step_inplace_f4 picks from 8 192
-    // bodies up (same sums, same order there), the static rules' T2 / T1 kernels below
+    // always the stream-K force kernel (the one with scratch): the tile shape the mid-size rule picks by unit balance
+    // from 8 192 bodies up, the static rules' T2 / T1 kernels below
     const int vid = n >= g_small_below ? mid_variant(n, n, sms) : n >= 2048 ? 3 : 12;
     const Variant* var = find_variant(vid);
     if (!var) return fail(NBODY_E_STATE, "kernel variant %d is not in this build", vid);

@@ -117,7 +117,7 @@ int nbody_snapshot_load(nbody_ctx* c, const char* path)
         return fail(NBODY_E_STATE, "%s was written with %s summation, the context uses the other one (nbody_params.summation)", path, (h.variant & 0x10000u) ? "single-level" : "two-level");
     if (h.version >= 2 && h.variant != 0 && c->kids.empty() && c->p.world == 1 && (int)(h.variant & 0xffffu) != c->var->id) {
         const Variant* sv = find_variant((int)(h.variant & 0xffffu));
-        const bool same_sums = sv && sv->small == c->var->small && sv->T == c->var->T && sv->NT == c->var->NT && sv->UJ == c->var->UJ && sv->cs == c->var->cs && sv->cmode == c->var->cmode;
+        const bool same_sums = sv && sv->small == c->var->small && sv->H == c->var->H && sv->T == c->var->T && sv->NT == c->var->NT && sv->UJ == c->var->UJ && sv->cs == c->var->cs && sv->cmode == c->var->cmode;
         if (!same_sums) {
             if (c->p.variant != NBODY_VARIANT_AUTO)
                 return fail(NBODY_E_STATE, "%s was written by kernel variant %u; the context was created with variant %d (other summation order): create it with NBODY_VARIANT_AUTO or that variant", path, h.variant & 0xffffu, c->p.variant);

@@ -135,13 +135,18 @@ def test_kernel_choice_rules_are_host_logic(nb):
     # NBODY_VARIANT_AUTO by size (DESIGN.md section 3 "Variant choice" / "Mid-size N"); host-only, no GPU involved
     names = nb.variants()
     pick = lambda t, s=None: nb.choose_variant(t, s or t)   # noqa: E731
-    assert names[pick(1024)[0]].startswith("S_TT2") and names[pick(8000)[0]].startswith("S_TT4")   # small-N family
-    assert pick(1024) == (85, False) and pick(3072) == (82, False) and pick(8191) == (82, False)
-    # mid sizes: tile shape x unit size by unit balance on 148 SMs (measured best in profiles/r1_small_family_sweep.jsonl
-    # and the runs recorded in DESIGN.md): N = 16 384 -> T8 x 128-body units, 32 768 -> T8 x 256, 50 000 -> T6 x 256
-    assert names[pick(16384)[0]].startswith("T8_NT256_UJ128") and names[pick(32768)[0]].startswith("T8_NT256_UJ256")
-    assert names[pick(50000)[0]].startswith("T6_NT256_UJ256")
+    assert names[pick(1024)[0]].startswith("S_TT2") and names[pick(3000)[0]].startswith("S_TT2")   # small-N family
+    assert pick(1024) == (85, False) and pick(2047) == (85, False)
+    # unsharded mid sizes whose whole target tiles fill 148 SMs evenly: row-split family (tile = T x H targets per CTA,
+    # one wave); 16 384 = BASELINE config 2 -> 147 tiles of 7 x 16
+    assert names[pick(16384)[0]].startswith("R_T7_H16") and names[pick(8192)[0]].startswith("R_T7_H8")
+    assert names[pick(4096)[0]].startswith("R_T7_H4") and names[pick(18944)[0]].startswith("R_T8_H16")
+    # ... otherwise the stream-K kernels, tile shape x unit size by unit balance (DESIGN.md section 3 "Mid-size N")
+    assert names[pick(20480)[0]].startswith("T8_NT256_UJ128") and names[pick(50000)[0]].startswith("T6_NT256_UJ256")
     assert all(not pick(n)[1] and not names[pick(n)[0]].startswith("S_") for n in (8192, 10240, 12288, 20000, 65535))
+    assert all(names[pick(n)[0]].startswith("T") for n in (10240, 12288, 20000, 40000, 65535))
+    # a shard never gets the row-split family (it has no in-kernel barrier)
+    assert names[pick(16384, 131072)[0]].startswith("T")
     # large: one of the equivalent kernels, timed on the device
     assert pick(65536)[1] and pick(1 << 20)[1] and pick(131072, 1 << 20)[1]
     # a shard with few targets of many sources: more CTAs per SM instead of more targets per thread

@@ -308,10 +308,13 @@ def test_large_contexts_pick_their_kernel_by_measurement(cuda, nb):
 
 
 def test_mid_size_contexts_pick_tile_shape_by_unit_balance(cuda, nb, oracle):
-    # 16 384 bodies: 8 tiles of 2048 targets x 128-body units = 1024 units = 6.9 per CTA (7 run) beats
-    # 11 tiles of 1536 (the last 2/3 empty) x 256-body units = 704 units = 4.76 per CTA (5 run)
-    with nb.Simulation(16384) as sim:
+    # 20 480 bodies: 10 tiles of 2048 targets x 128-body units = 1600 units = 10.8 per CTA (11 run) beats
+    # 14 tiles of 1536 (the last 1/3 empty) x 256-body units = 1120 units = 7.6 per CTA (8 run);
+    # 16 384 = 147 whole tiles of 112 targets: the row-split family, where no tile is shared between CTAs
+    with nb.Simulation(20480) as sim:
         assert sim.info()["variant_name"].startswith("T8_NT256_UJ128")
+    with nb.Simulation(16384) as sim:
+        assert sim.info()["variant_name"].startswith("R_T7_H16")
     with nb.Simulation(50000) as sim:
         assert sim.info()["variant_name"].startswith("T6_NT256_UJ256")
         x0 = nb.ic_uniform(50000, seed=2)

@@ -44,8 +44,9 @@ def test_exported_and_refuses_sizes_beyond_the_static_scratch(nb):
     assert nb.lib.nbody_step_inplace_noalloc_f4(1, 1, 1, 16, 0.0, DT, None) == -1
 
 
-# 16 384 = the maximum (BASELINE config 2; same kernel shape as the existing entry point); 10 000: ragged, split
-# tiles; 3 000 / 700: below 8 192 the existing entry point runs its small-N kernels (other summation order)
+# 16 384 = the maximum (BASELINE config 2); 10 000: ragged, split tiles; 3 000 / 700: small systems.  The existing
+# entry point picks its kernel by size (small-N, row-split or stream-K family); the allocation-free one always runs the
+# stream-K kernel, so the two agree to summation rounding, not bit for bit
 @pytest.mark.gpu
 @pytest.mark.parametrize("n", [16384, 10000, 3000, 700])
 def test_two_calls_in_a_row_match_the_existing_entry_point(cuda, nb, n):
@@ -71,8 +72,6 @@ def test_two_calls_in_a_row_match_the_existing_entry_point(cuda, nb, n):
         assert norm_rel_err(vn.cpu().numpy(), vr.cpu().numpy()) <= TOL_V
         assert norm_rel_err(xn.cpu().numpy(), xr.cpu().numpy()) <= TOL_X
         assert torch.equal(xn[:, 3], xr[:, 3]) and float(an[:, 3].abs().max()) == 0.0   # mass untouched, A.w = 0
-    if n >= 8192:   # same kernel shape, same sums in the same order
-        assert torch.equal(xn, xr) and torch.equal(vn, vr) and torch.equal(an, ar)
 
 
 @pytest.mark.gpu
