@@ -94,6 +94,8 @@ struct Variant {
 // row-split family (mid-size N that divides evenly over the SMs): T x H targets per CTA, no scratch
 #define RVARIANT(id, T, H, UJ, UN, ORD) \
     { id, "R_T" #T "_H" #H "_NT256_UJ" #UJ "_U" #UN "_" #ORD, T, 256, UJ, UN, 1, 1, 1, 0, rowsplit_kernel<T, H, 256, UJ, UN, ORD>, nullptr, nullptr, nullptr, 2, H, rowsplit_kernel<T, H, 256, UJ, UN, ORD, 1> }
+#define RVARIANT_L(id, T, H, UJ, UN, ORD, LOOK) \
+    { id, "R_T" #T "_H" #H "_NT256_UJ" #UJ "_U" #UN "_" #ORD "_L" #LOOK, T, 256, UJ, UN, 1, 1, 1, 0, rowsplit_kernel<T, H, 256, UJ, UN, ORD, 0, LOOK>, nullptr, nullptr, nullptr, 2, H, rowsplit_kernel<T, H, 256, UJ, UN, ORD, 1, LOOK> }
 // packed: 0 = scalar FFMA path (kept as the with/without evidence of the f32x2 choice), 1 = FADD2/FMUL2/FFMA2,
 // 5 / 6 / 7 / 8 = the same packed arithmetic in another source order (bit-identical results; ptxas' register
 // allocation differs by a few per cent, see tuned_large_variant).
@@ -191,7 +193,14 @@ const Variant kVariants[] = {
     RVARIANT(181, 7, 16, 512, 2, 0),
     RVARIANT(182, 7, 16, 256, 2, 0),
     RVARIANT(183, 7, 16, 512, 8, 0),
-    RVARIANT(184, 7, 16, 1024, 4, 5),
+    RVARIANT(185, 7, 16, 1024, 4, 1),
+    RVARIANT(187, 7, 16, 1024, 4, 8),
+    RVARIANT(188, 7, 16, 1024, 4, 9),
+    RVARIANT(189, 7, 16, 1024, 4, 13),
+    RVARIANT(190, 7, 16, 1024, 2, 0),
+    RVARIANT_L(191, 7, 16, 1024, 4, 0, 3),
+    RVARIANT_L(192, 7, 16, 1024, 4, 0, 1),
+    RVARIANT(186, 7, 16, 1024, 4, 5),         // source orders, unroll 2 and ring look-ahead 3 / 1 at UJ 1024: none beats 152
     SVARIANT(80, 8, 128, 2),
     SVARIANT(81, 8, 256, 2),
     SVARIANT(83, 16, 256, 1),

@@ -759,7 +759,7 @@ __global__ void __launch_bounds__(NT) small_kernel(const ForceArgs a)
 // TRIM 1: the zero-mass padding behind the last real body of the last unit is skipped (ForceArgs.last_unit_bodies); a
 // separate instantiation, launched only when N is not a multiple of the unit: with the variable trip count in the
 // code ptxas allocates the common loop differently (N = 16 384: 104.8 us instead of 103.6).  Same sums either way.
-template <int T, int H, int NT, int UJ, int UNROLL, int ORD = 0, int TRIM = 0>
+template <int T, int H, int NT, int UJ, int UNROLL, int ORD = 0, int TRIM = 0, int LOOK = kLookahead>
 __global__ void __launch_bounds__(NT, 1) rowsplit_kernel(const ForceArgs a)
 {
     constexpr int SUB = 32 / H, NW = NT / 32, SPLIT = SUB * NW, TI = T * H;
@@ -797,7 +797,7 @@ __global__ void __launch_bounds__(NT, 1) rowsplit_kernel(const ForceArgs a)
         ++pj; ++kf;
     };
     if (tid == 0)
-        for (int i = 0; i < kLookahead; ++i) issue();
+        for (int i = 0; i < LOOK; ++i) issue();
 
     const int g0 = blockIdx.x * TI;
     u64 nx[T], ny[T], nz[T], ax[T], ay[T], az[T];
@@ -823,10 +823,11 @@ __global__ void __launch_bounds__(NT, 1) rowsplit_kernel(const ForceArgs a)
             for (int q = 0; q < UNROLL; ++q) {
                 const ulonglong2 xy = sp[2 * SPLIT * (i + q)], zm = sp[2 * SPLIT * (i + q) + 1];   // (x0,x1)(y0,y1) | (z0,z1)(m0,m1)
 #pragma unroll
-                for (int t = 0; t < T; ++t) {
+                for (int tt = 0; tt < T; ++tt) {
+                    const int t = ORD >= 8 ? T - 1 - tt : tt;   // source order only: the same sums either way
                     u64 dx, dy, dz;
-                    if (ORD == 1) { dz = add2(zm.x, nz[t]); dy = add2(xy.y, ny[t]); dx = add2(xy.x, nx[t]); }
-                    else if (ORD == 5) { dx = add2(xy.x, nx[t]); dz = add2(zm.x, nz[t]); dy = add2(xy.y, ny[t]); }
+                    if ((ORD & 7) == 1) { dz = add2(zm.x, nz[t]); dy = add2(xy.y, ny[t]); dx = add2(xy.x, nx[t]); }
+                    else if ((ORD & 7) == 5) { dx = add2(xy.x, nx[t]); dz = add2(zm.x, nz[t]); dy = add2(xy.y, ny[t]); }
                     else { dx = add2(xy.x, nx[t]); dy = add2(xy.y, ny[t]); dz = add2(zm.x, nz[t]); }
                     u64 r2 = fma2(dx, dx, eps2p);
                     r2 = fma2(dy, dy, r2);
@@ -835,8 +836,8 @@ __global__ void __launch_bounds__(NT, 1) rowsplit_kernel(const ForceArgs a)
                     float lo, hi;
                     unpack2(d3, lo, hi);
                     const u64 sc = mul2(pack2(rsqrt_mufu(lo), rsqrt_mufu(hi)), zm.y);
-                    if (ORD == 1) { az[t] = fma2(dz, sc, az[t]); ay[t] = fma2(dy, sc, ay[t]); ax[t] = fma2(dx, sc, ax[t]); }
-                    else if (ORD == 5) { ax[t] = fma2(dx, sc, ax[t]); az[t] = fma2(dz, sc, az[t]); ay[t] = fma2(dy, sc, ay[t]); }
+                    if ((ORD & 7) == 1) { az[t] = fma2(dz, sc, az[t]); ay[t] = fma2(dy, sc, ay[t]); ax[t] = fma2(dx, sc, ax[t]); }
+                    else if ((ORD & 7) == 5) { ax[t] = fma2(dx, sc, ax[t]); az[t] = fma2(dz, sc, az[t]); ay[t] = fma2(dy, sc, ay[t]); }
                     else { ax[t] = fma2(dx, sc, ax[t]); ay[t] = fma2(dy, sc, ay[t]); az[t] = fma2(dz, sc, az[t]); }
                 }
             }
