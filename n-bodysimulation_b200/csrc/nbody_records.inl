@@ -113,8 +113,14 @@ int nbody_snapshot_load(nbody_ctx* c, const char* path)
     if (h.version >= 2 && h.checksum != fnv1a(v.data(), nb, fnv1a(x.data(), nb)))
         return fail(NBODY_E_INVALID, "%s: payload checksum mismatch (corrupted file)", path);
     // bit-identical resume: run the kernel the saver ran (same tile shape and unit size = same summation order)
-    if (h.version >= 2 && h.variant != 0 && c->kids.empty() && c->p.world == 1 && ((h.variant & 0x10000u) != 0) != c->plan_full.single)
-        return fail(NBODY_E_STATE, "%s was written with %s summation, the context uses the other one (nbody_params.summation)", path, (h.variant & 0x10000u) ? "single-level" : "two-level");
+    // (the summation flag is compared with what THIS context would run on the saver's kernel: the small-N and row-split
+    // families have one summation only and always write 0)
+    if (h.version >= 2 && h.variant != 0 && c->kids.empty() && c->p.world == 1) {
+        const Variant* sv = find_variant((int)(h.variant & 0xffffu));
+        const bool would_be_single = c->p.summation == NBODY_SUM_SINGLE && (sv ? sv->kernel_single != nullptr : c->plan_full.single);
+        if (((h.variant & 0x10000u) != 0) != would_be_single)
+            return fail(NBODY_E_STATE, "%s was written with %s summation, the context uses the other one (nbody_params.summation)", path, (h.variant & 0x10000u) ? "single-level" : "two-level");
+    }
     if (h.version >= 2 && h.variant != 0 && c->kids.empty() && c->p.world == 1 && (int)(h.variant & 0xffffu) != c->var->id) {
         const Variant* sv = find_variant((int)(h.variant & 0xffffu));
         const bool same_sums = sv && sv->small == c->var->small && sv->H == c->var->H && sv->T == c->var->T && sv->NT == c->var->NT && sv->UJ == c->var->UJ && sv->cs == c->var->cs && sv->cmode == c->var->cmode;

@@ -70,3 +70,30 @@ def test_in_place_simulate_uses_it_too(cuda, nb, oracle):
     nb.simulate(dx, da, dv, n)                                  # kernel.cuh:2
     (x, v, a), _ = one_step(nb, x0)
     assert np.array_equal(da.cpu().numpy(), a) and np.array_equal(dx.cpu().numpy(), x)
+
+
+def test_snapshots_of_a_row_split_run(cuda, nb, tmp_path):
+    # the family has one summation only: a file it wrote resumes bit-identically whatever nbody_params.summation says,
+    # and a file a stream-K kernel wrote re-pins that kernel (csrc/nbody_records.inl)
+    n = 16384
+    x0, v0 = nb.ic_plummer(n, seed=8)
+    path, path_sk = str(tmp_path / "row.nbody"), str(tmp_path / "sk.nbody")
+    with nb.Simulation(n, eps2=1e-4, dt=1e-3) as sim:
+        sim.upload(x0, v0).step(3).save(path).step(2)
+        straight = sim.download()
+    for summation in (nb.NBODY_SUM_TWO_LEVEL, nb.NBODY_SUM_SINGLE):
+        with nb.Simulation(n, eps2=1e-4, dt=1e-3, summation=summation) as sim:
+            sim.load(path).step(2)
+            assert sim.info()["variant_name"].startswith("R_T7_H16") and sim.steps_done() == 5
+            for p, q in zip(straight, sim.download()):
+                assert np.array_equal(p, q)
+    with nb.Simulation(n, eps2=1e-4, dt=1e-3, variant=110, summation=nb.NBODY_SUM_SINGLE) as sim:
+        sim.upload(x0, v0).step(3).save(path_sk).step(2)
+        straight_sk = sim.download()
+    with nb.Simulation(n, eps2=1e-4, dt=1e-3, summation=nb.NBODY_SUM_SINGLE) as sim:     # AUTO = row-split; the file says stream-K
+        sim.load(path_sk).step(2)
+        assert sim.info()["variant_name"].startswith("T8_NT256_UJ128")
+        for p, q in zip(straight_sk, sim.download()):
+            assert np.array_equal(p, q)
+    with nb.Simulation(n, eps2=1e-4, dt=1e-3) as sim, pytest.raises(nb.NBodyError, match="summation"):
+        sim.load(path_sk)                                        # two-level context, single-level file
