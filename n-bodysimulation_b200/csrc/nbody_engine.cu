@@ -142,6 +142,9 @@ const Variant kVariants[] = {
     RVARIANT(165, 6, 4, 1024, 4, 0),
     RVARIANT(166, 7, 4, 1024, 4, 0),
     RVARIANT(167, 8, 4, 1024, 4, 0),
+    RVARIANT(154, 9, 16, 1024, 4, 0),        // T = 9 (242 registers) closes the gaps between the lane classes: tiles of 36, 72, 144
+    RVARIANT(164, 9, 8, 1024, 4, 0),
+    RVARIANT(168, 9, 4, 1024, 4, 0),
     RVARIANT(170, 5, 32, 1024, 4, 0),
     RVARIANT(171, 6, 32, 1024, 4, 0),
     RVARIANT(172, 7, 32, 1024, 4, 0),
@@ -243,9 +246,9 @@ const int g_small_below = env_int("NBODY_SMALL_BELOW", 8192);
 int round_up(int v, int m) { return (v + m - 1) / m * m; }
 struct RowCand { int id, T, H; double rate; };
 const RowCand kRowCands[] = {
-    {165, 6, 4, 2500.}, {166, 7, 4, 2500.}, {167, 8, 4, 2500.},
-    {160, 5, 8, 2500.}, {161, 6, 8, 2640.}, {162, 7, 8, 2620.}, {163, 8, 8, 2645.},
-    {150, 5, 16, 2550.}, {151, 6, 16, 2600.}, {152, 7, 16, 2690.}, {153, 8, 16, 2600.},
+    {165, 6, 4, 2500.}, {166, 7, 4, 2500.}, {167, 8, 4, 2500.}, {168, 9, 4, 2450.},
+    {160, 5, 8, 2500.}, {161, 6, 8, 2640.}, {162, 7, 8, 2620.}, {163, 8, 8, 2645.}, {164, 9, 8, 2600.},
+    {150, 5, 16, 2550.}, {151, 6, 16, 2600.}, {152, 7, 16, 2690.}, {153, 8, 16, 2600.}, {154, 9, 16, 2600.},
     {170, 5, 32, 2625.}, {171, 6, 32, 2640.}, {172, 7, 32, 2680.}, {173, 8, 32, 2645.},
 };
 const bool g_rowsplit = getenv("NBODY_NO_ROWSPLIT") == nullptr;   // with / without switch of the experiments

@@ -141,10 +141,11 @@ def test_kernel_choice_rules_are_host_logic(nb):
     # one wave); 16 384 = BASELINE config 2 -> 147 tiles of 7 x 16
     assert names[pick(16384)[0]].startswith("R_T7_H16") and names[pick(8192)[0]].startswith("R_T7_H8")
     assert names[pick(4096)[0]].startswith("R_T7_H4") and names[pick(18944)[0]].startswith("R_T8_H16")
+    assert names[pick(10240)[0]].startswith("R_T9_H8") and names[pick(20480)[0]].startswith("R_T9_H16")
     # ... otherwise the stream-K kernels, tile shape x unit size by unit balance (DESIGN.md section 3 "Mid-size N")
-    assert names[pick(20480)[0]].startswith("T8_NT256_UJ128") and names[pick(50000)[0]].startswith("T6_NT256_UJ256")
-    assert all(not pick(n)[1] and not names[pick(n)[0]].startswith("S_") for n in (8192, 10240, 12288, 20000, 65535))
-    assert all(names[pick(n)[0]].startswith("T") for n in (12288, 17500, 20000, 26000, 40000, 65535))
+    assert names[pick(22000)[0]].startswith("T8_NT256_UJ128") and names[pick(50000)[0]].startswith("T6_NT256_UJ256")
+    assert all(not pick(n)[1] and not names[pick(n)[0]].startswith("S_") for n in (8192, 10240, 12288, 22000, 65535))
+    assert all(names[pick(n)[0]].startswith("T") for n in (12288, 17500, 22000, 26000, 40000, 65535))
     # a shard never gets the row-split family (it has no in-kernel barrier)
     assert names[pick(16384, 131072)[0]].startswith("T")
     # large: one of the equivalent kernels, timed on the device

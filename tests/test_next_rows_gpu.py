@@ -308,10 +308,10 @@ def test_large_contexts_pick_their_kernel_by_measurement(cuda, nb):
 
 
 def test_mid_size_contexts_pick_tile_shape_by_unit_balance(cuda, nb, oracle):
-    # 20 480 bodies: 10 tiles of 2048 targets x 128-body units = 1600 units = 10.8 per CTA (11 run) beats
-    # 14 tiles of 1536 (the last 1/3 empty) x 256-body units = 1120 units = 7.6 per CTA (8 run);
+    # 22 000 bodies: 11 tiles of 2048 targets x 128-body units = 1892 units = 12.8 per CTA (13 run) beats
+    # 15 tiles of 1536 (the last 2/3 empty) x 256-body units = 1290 units = 8.7 per CTA (9 run);
     # 16 384 = 147 whole tiles of 112 targets: the row-split family, where no tile is shared between CTAs
-    with nb.Simulation(20480) as sim:
+    with nb.Simulation(22000) as sim:
         assert sim.info()["variant_name"].startswith("T8_NT256_UJ128")
     with nb.Simulation(16384) as sim:
         assert sim.info()["variant_name"].startswith("R_T7_H16")
