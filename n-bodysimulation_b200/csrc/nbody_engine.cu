@@ -271,7 +271,8 @@ int static_variant(int n_targets, int n_sources, int sms, bool* measured)
     *measured = false;
     if (g_rowsplit && n_targets == n_sources && n_sources >= 2048 && n_sources < 65536) {
         // unsharded mid-size system: row-split where its whole tiles fill the SMs well enough to beat the others'
-        // measured times (small-N family: N^2 / 1.9e6 + 3.2 us; stream-K kernels: 1.04 N^2 / 2.69e6 + 12 us on 148 SMs;
+        // measured times (small-N family: N^2 / 0.95e6 + 0.7 us below 3 072 bodies, N^2 / 1.9e6 + 3.2 us above; stream-K
+        // kernels: 1.04 N^2 / 2.69e6 + 12 us on 148 SMs;
         // both a little optimistic for the others, so a tie goes to them)
         if (sms <= 0) {
             int dev = 0;
@@ -281,7 +282,9 @@ int static_variant(int n_targets, int n_sources, int sms, bool* measured)
         double t_row = 0.0;
         const int id = row_variant(n_sources, sms, &t_row);
         const double n2 = (double)n_sources * (double)n_sources;
-        const double t_other = n_sources < g_small_below ? n2 / 1.9e6 + 3.2 : 1.04 * n2 / (2.69e6 * sms / 148.0) + 12.0;
+        const double t_other = n_sources < 3072 ? n2 / 0.95e6 + 0.7                       // small-N family, 2 targets per CTA
+                               : n_sources < g_small_below ? n2 / 1.9e6 + 3.2            // ... 4 targets per CTA
+                                                           : 1.04 * n2 / (2.69e6 * sms / 148.0) + 12.0;
         if (id && t_row < 0.99 * t_other) return id;
     }
     if (n_sources < g_small_below) {     // a step is < 50 us: latency decides -> small-N family

@@ -135,7 +135,8 @@ def test_kernel_choice_rules_are_host_logic(nb):
     # NBODY_VARIANT_AUTO by size (DESIGN.md section 3 "Variant choice" / "Mid-size N"); host-only, no GPU involved
     names = nb.variants()
     pick = lambda t, s=None: nb.choose_variant(t, s or t)   # noqa: E731
-    assert names[pick(1024)[0]].startswith("S_TT2") and names[pick(3000)[0]].startswith("S_TT2")   # small-N family
+    assert names[pick(1024)[0]].startswith("S_TT2") and names[pick(2300)[0]].startswith("S_TT2")   # small-N family
+    assert names[pick(3200)[0]].startswith("S_TT4") and names[pick(3000)[0]].startswith("R_T6_H4")
     assert pick(1024) == (85, False) and pick(2047) == (85, False)
     # unsharded mid sizes whose whole target tiles fill 148 SMs evenly: row-split family (tile = T x H targets per CTA,
     # one wave); 16 384 = BASELINE config 2 -> 147 tiles of 7 x 16
