@@ -662,7 +662,7 @@ def run_ours(args):
     if rank == 0 and not args.no_extras:
         if world == 1:
             small_n = []
-            for nn, st in ((16384, 400), (131072, 20)):
+            for nn, st in ((8192, 800), (16384, 400), (131072, 20)):   # 8 192 = the reference's shipped N_BODIES (constants.h:13), 16 384 = config 2, 131 072 = config 3
                 with nb.Simulation(nn, device=local) as s:
                     s.upload(nb.ic_uniform(nn, seed=12345)).step(max(st // 10, 2))
                     s.step(st)
