@@ -12,14 +12,17 @@ run 3552 640 0 165
 run 4144 640 0 166
 run 4096 640 0 166
 run 4736 640 0 167
+run 5328 640 0 168
 run 5920 640 0 160
 run 7104 640 0 161
 run 8288 640 0 162
 run 8192 640 0 162
 run 9472 640 0 163
+run 10656 640 0 164
 run 11840 640 0 150
 run 14208 640 0 151
 run 18944 640 0 153
+run 21312 320 0 154
 run 23680 320 0 170
 run 28416 320 0 171
 run 33152 320 0 172
