@@ -157,3 +157,25 @@ def test_kernel_choice_rules_are_host_logic(nb):
         nb.choose_variant(0, 10)
     with pytest.raises(nb.NBodyError):
         nb.choose_variant(20, 10)
+
+
+def test_row_split_rule_only_takes_whole_single_waves(nb):
+    # the row-split family runs one CTA per tile of T x H targets: NBODY_VARIANT_AUTO may take it only where the tiles
+    # fit one wave of the 148 SMs and fill most of it (measured never slower there, profiles/r2_rowsplit.txt), and
+    # never for a shard (it has no in-kernel barrier)
+    names = nb.variants()
+    picked = 0
+    for n in range(2048, 65536, 61):
+        name = names[nb.choose_variant(n, n)[0]]
+        m = re.match(r"R_T(\d+)_H(\d+)_", name)
+        if not m:
+            continue
+        picked += 1
+        tile = int(m.group(1)) * int(m.group(2))
+        assert -(-n // tile) <= 148, (n, name)
+        assert n / (148.0 * tile) >= (0.85 if n >= 8192 else 0.68), (n, name)
+    assert picked > 100
+    assert names[nb.choose_variant(40000, 40000)[0]].startswith("T") and names[nb.choose_variant(65535, 65535)[0]].startswith("T")
+    for targets in (4096, 8192, 16384, 32768):
+        for sources in (65536, 131072, 1 << 20):
+            assert not names[nb.choose_variant(targets, sources)[0]].startswith("R_")
