@@ -228,6 +228,8 @@ void nbody_release_cached(void);
  *   - n <= nbody_noalloc_max_bodies() = 16 384; larger n is refused with NBODY_E_INVALID (use the call above).
  *   - the work is ENQUEUED on `stream` (a cudaStream_t passed as void*, NULL = the legacy default stream) on the
  *     current device; the call does not synchronise.
+ *   - the first call on a device asks the runtime for the array's address and sets the kernels' attributes (no
+ *     allocation, but not stream work either): make that call outside a stream capture.
  *   - all calls on one GPU share the array: calls that can overlap on the GPU (different streams, threads,
  *     graphs replayed side by side) race on it -- serialise them.  Nothing is assumed about the array's contents
  *     between calls (the counters are cleared on `stream` before each step).
